@@ -1,0 +1,378 @@
+// msda_api.cu -- extern "C" entry points of libmsda_sm100.so (declared in include/msda.h).
+//
+// Host-side role of the reference's ms_deform_attn_cuda_forward / _backward
+// (pdvc/ops/src/cuda/ms_deform_attn_cuda.cu:20-80, :83-153): validate, pick a kernel, launch on the
+// caller's stream.  Unlike the reference there is no ATen, no allocation, no per-64-sample host loop
+// (cu:61-75) and no silent printf on launch failure (ms_deform_im2col_cuda.cuh:949-953): errors come
+// back as return codes.
+#include <cstdio>
+
+#include "msda_fast.cuh"
+#include "msda_generic.cuh"
+
+using namespace msda;
+
+namespace {
+
+thread_local int g_launches = 0;
+
+constexpr int kNumSMs = 148;   // B200; grids are sized in multiples of it
+
+inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+inline int check_launch()
+{
+    ++g_launches;
+    const cudaError_t e = cudaGetLastError();
+    return (int)e;
+}
+
+struct Dims {
+    int N, S, M, D, L, Lq, P;
+};
+
+int check_dims(const Dims &d, int dtype, int pad_mode)
+{
+    if (dtype != MSDA_F32 && dtype != MSDA_BF16 && dtype != MSDA_F64) return MSDA_ERR_DTYPE;
+    if (pad_mode != MSDA_PAD_BORDER && pad_mode != MSDA_PAD_ZEROS) return MSDA_ERR_PAD;
+    if (d.N <= 0 || d.S <= 0 || d.M <= 0 || d.D <= 0 || d.L <= 0 || d.Lq <= 0 || d.P <= 0) return MSDA_ERR_SHAPE;
+    if (d.L > MSDA_MAX_LEVELS) return MSDA_ERR_SHAPE;
+    // per-sample offsets are 32-bit inside the kernels
+    if ((long long)d.S * d.M * d.D >= (1ll << 31)) return MSDA_ERR_SHAPE;
+    if ((long long)d.L * d.P >= (1 << 20)) return MSDA_ERR_SHAPE;
+    // unit indices (n,q,m) are 32-bit inside the vectorised kernels
+    if ((long long)d.N * d.Lq * d.M >= (1ll << 30)) return MSDA_ERR_SHAPE;
+    return MSDA_OK;
+}
+
+
+// lanes per unit for the vectorised path, or 0 if (D, dtype) is not eligible
+int fast_lpg(int D, int dtype)
+{
+    const int ch = dtype == MSDA_BF16 ? 8 : 4;
+    if (dtype == MSDA_F64 || D % ch != 0) return 0;
+    const int lanes = D / ch;
+    if (lanes < 4) return 0;
+    if (lanes >= 32) return (D % (32 * ch) == 0) ? 32 : 0;   // D chunks of 32 lanes each
+    int p = 4;
+    while (p < lanes) p <<= 1;
+    return p;   // 4, 8, 16 or 32 (with masked lanes if lanes is not a power of two)
+}
+
+void fast_grid(int total_units, int lpg, int &grid, int &units_per_cta)
+{
+    const int g = 32 / lpg;
+    const long long per_iter = (long long)kFastWarps * g;   // units one CTA covers per loop trip
+    long long ctas = (total_units + per_iter - 1) / per_iter;
+    const long long cap = (long long)kNumSMs * 16;          // <= 16 resident 128-thread CTAs per SM
+    if (ctas > cap) ctas = cap;
+    long long upc = (total_units + ctas - 1) / ctas;
+    upc = (upc + per_iter - 1) / per_iter * per_iter;
+    grid = (int)((total_units + upc - 1) / upc);
+    units_per_cta = (int)upc;
+}
+
+template <typename VT, bool FUSED> int launch_fast_fwd(const FastArgs &a, int lpg, int grid, cudaStream_t st)
+{
+    switch (lpg) {
+        case 4: msda_fwd_fast_kernel<VT, 4, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
+        case 8: msda_fwd_fast_kernel<VT, 8, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
+        case 16: msda_fwd_fast_kernel<VT, 16, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
+        default: msda_fwd_fast_kernel<VT, 32, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
+    }
+    return check_launch();
+}
+
+template <typename VT, bool FUSED> int launch_fast_bwd(const FastArgs &a, int lpg, int grid, cudaStream_t st)
+{
+    switch (lpg) {
+        case 4: msda_bwd_fast_kernel<VT, 4, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
+        case 8: msda_bwd_fast_kernel<VT, 8, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
+        case 16: msda_bwd_fast_kernel<VT, 16, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
+        default: msda_bwd_fast_kernel<VT, 32, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
+    }
+    return check_launch();
+}
+
+int generic_grid(long long total)
+{
+    long long blocks = (total + 255) / 256;
+    const long long cap = (long long)kNumSMs * 32;
+    return (int)(blocks > cap ? cap : blocks);
+}
+
+template <bool SAMPLER> int launch_generic_fwd(const GenericArgs &a, int dtype, cudaStream_t st)
+{
+    const int grid = generic_grid(a.total);
+    if (dtype == MSDA_F32) msda_fwd_generic_kernel<float, SAMPLER><<<grid, 256, 0, st>>>(a);
+    else if (dtype == MSDA_F64) msda_fwd_generic_kernel<double, SAMPLER><<<grid, 256, 0, st>>>(a);
+    else msda_fwd_generic_kernel<__nv_bfloat16, SAMPLER><<<grid, 256, 0, st>>>(a);
+    return check_launch();
+}
+
+template <bool SAMPLER> int launch_generic_bwd(const GenericArgs &a, int dtype, cudaStream_t st)
+{
+    const int grid = generic_grid(a.total);
+    if (dtype == MSDA_F32) msda_bwd_generic_kernel<float, SAMPLER><<<grid, 256, 0, st>>>(a);
+    else if (dtype == MSDA_F64) msda_bwd_generic_kernel<double, SAMPLER><<<grid, 256, 0, st>>>(a);
+    else msda_bwd_generic_kernel<__nv_bfloat16, SAMPLER><<<grid, 256, 0, st>>>(a);
+    return check_launch();
+}
+
+int memset_async(void *p, size_t bytes, cudaStream_t st)
+{
+    ++g_launches;
+    return (int)cudaMemsetAsync(p, 0, bytes, st);
+}
+
+// bf16: turn the fp32 accumulation image into grad_value
+int finish_bf16(const float *acc, void *grad_value, long long n, cudaStream_t st)
+{
+    if (n % 8 == 0) {
+        const long long n8 = n / 8;
+        long long blocks = (n8 + 255) / 256;
+        if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+        msda_cvt_f32_to_bf16_kernel<<<(int)blocks, 256, 0, st>>>(acc, static_cast<__nv_bfloat16 *>(grad_value), n8);
+    } else {
+        msda_cvt_f32_to_bf16_scalar_kernel<<<generic_grid(n), 256, 0, st>>>(acc, static_cast<__nv_bfloat16 *>(grad_value), n);
+    }
+    return check_launch();
+}
+
+}  // namespace
+
+extern "C" {
+
+int msda_version(void) { return MSDA_VERSION; }
+const char *msda_arch(void) { return "sm_100a"; }
+int msda_last_launch_count(void) { return g_launches; }
+
+const char *msda_error_string(int code)
+{
+    switch (code) {
+        case MSDA_OK: return "success";
+        case MSDA_ERR_DTYPE: return "msda: unsupported dtype for this entry point";
+        case MSDA_ERR_SHAPE: return "msda: invalid or out-of-range dimension";
+        case MSDA_ERR_NULL: return "msda: required pointer is NULL";
+        case MSDA_ERR_ALIGN: return "msda: tensor base pointer must be 16-byte aligned";
+        case MSDA_ERR_WORKSPACE: return "msda: workspace too small (see msda_backward_workspace_bytes)";
+        case MSDA_ERR_PAD: return "msda: unknown pad_mode";
+        case MSDA_ERR_UNSUPPORTED: return "msda: combination not supported";
+        default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "msda: unknown error";
+    }
+}
+
+size_t msda_backward_workspace_bytes(int N, int S, int M, int D, int dtype)
+{
+    if (dtype != MSDA_BF16) return 0;
+    return (size_t)N * S * M * D * sizeof(float);
+}
+
+int msda_ms_deform_attn_forward(const void *value, const int64_t *spatial_shapes, const int64_t *level_start_index,
+                                const void *sampling_loc, const void *attn_weight, void *output, int N, int S, int M,
+                                int D, int L, int Lq, int P, int dtype, int pad_mode, unsigned flags, void *stream)
+{
+    g_launches = 0;
+    const Dims d{N, S, M, D, L, Lq, P};
+    if (int e = check_dims(d, dtype, pad_mode)) return e;
+    if (!value || !spatial_shapes || !level_start_index || !sampling_loc || !attn_weight || !output) return MSDA_ERR_NULL;
+    if (!aligned16(value) || !aligned16(sampling_loc) || !aligned16(attn_weight) || !aligned16(output)) return MSDA_ERR_ALIGN;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool one_d = (flags & MSDA_FLAG_ASSUME_1D) != 0;
+    const int lpg = (flags & MSDA_FLAG_FORCE_GENERIC) ? 0 : fast_lpg(D, dtype);
+    if (one_d && lpg) {
+        FastArgs a{};
+        a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
+        a.loc = static_cast<const float *>(sampling_loc); a.attn = static_cast<const float *>(attn_weight);
+        a.out = output;
+        a.N = N; a.S = S; a.M = M; a.D = D; a.L = L; a.Lq = Lq; a.P = P; a.pad_mode = pad_mode;
+        a.total_units = N * Lq * M;
+        int grid;
+        fast_grid(a.total_units, lpg, grid, a.units_per_cta);
+        return dtype == MSDA_F32 ? launch_fast_fwd<float, false>(a, lpg, grid, st)
+                                 : launch_fast_fwd<__nv_bfloat16, false>(a, lpg, grid, st);
+    }
+    GenericArgs a{};
+    a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
+    a.loc = sampling_loc; a.attn = attn_weight; a.out = output;
+    a.N = N; a.S = S; a.M = M; a.D = D; a.L = L; a.Lq = Lq; a.P = P; a.pad_mode = pad_mode;
+    a.assume_1d = one_d ? 1 : 0;
+    a.total = (long long)N * Lq * M * D;
+    return launch_generic_fwd<false>(a, dtype, st);
+}
+
+int msda_ms_deform_attn_backward(const void *value, const int64_t *spatial_shapes, const int64_t *level_start_index,
+                                 const void *sampling_loc, const void *attn_weight, const void *grad_output,
+                                 void *grad_value, void *grad_sampling_loc, void *grad_attn_weight, void *workspace,
+                                 size_t workspace_bytes, int N, int S, int M, int D, int L, int Lq, int P, int dtype,
+                                 int pad_mode, unsigned flags, void *stream)
+{
+    g_launches = 0;
+    const Dims d{N, S, M, D, L, Lq, P};
+    if (int e = check_dims(d, dtype, pad_mode)) return e;
+    if (!value || !spatial_shapes || !level_start_index || !sampling_loc || !attn_weight || !grad_output || !grad_value ||
+        !grad_sampling_loc || !grad_attn_weight)
+        return MSDA_ERR_NULL;
+    if (!aligned16(value) || !aligned16(sampling_loc) || !aligned16(attn_weight) || !aligned16(grad_output) ||
+        !aligned16(grad_value) || !aligned16(grad_sampling_loc) || !aligned16(grad_attn_weight))
+        return MSDA_ERR_ALIGN;
+    const size_t need = msda_backward_workspace_bytes(N, S, M, D, dtype);
+    if (need && (!workspace || workspace_bytes < need || !aligned16(workspace))) return MSDA_ERR_WORKSPACE;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const long long nv = (long long)N * S * M * D;
+    const long long ns = (long long)N * Lq * M * L * P;
+    const size_t ct = dtype == MSDA_F64 ? 8 : 4;   // element size of loc / attn and their grads
+    void *acc = dtype == MSDA_BF16 ? workspace : grad_value;
+    if (int e = memset_async(acc, (size_t)nv * (dtype == MSDA_F64 ? 8 : 4), st)) return e;
+    const bool one_d = (flags & MSDA_FLAG_ASSUME_1D) != 0;
+    const int lpg = (flags & MSDA_FLAG_FORCE_GENERIC) ? 0 : fast_lpg(D, dtype);
+    int rc;
+    if (one_d && lpg) {
+        FastArgs a{};
+        a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
+        a.loc = static_cast<const float *>(sampling_loc); a.attn = static_cast<const float *>(attn_weight);
+        a.grad_out = grad_output; a.gv_acc = static_cast<float *>(acc);
+        a.grad_loc = static_cast<float *>(grad_sampling_loc); a.grad_attn = static_cast<float *>(grad_attn_weight);
+        a.N = N; a.S = S; a.M = M; a.D = D; a.L = L; a.Lq = Lq; a.P = P; a.pad_mode = pad_mode;
+        a.total_units = N * Lq * M;
+        int grid;
+        fast_grid(a.total_units, lpg, grid, a.units_per_cta);
+        rc = dtype == MSDA_F32 ? launch_fast_bwd<float, false>(a, lpg, grid, st)
+                               : launch_fast_bwd<__nv_bfloat16, false>(a, lpg, grid, st);
+    } else {
+        if (int e = memset_async(grad_sampling_loc, (size_t)ns * 2 * ct, st)) return e;
+        if (int e = memset_async(grad_attn_weight, (size_t)ns * ct, st)) return e;
+        GenericArgs a{};
+        a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
+        a.loc = sampling_loc; a.attn = attn_weight; a.grad_out = grad_output;
+        a.gv_acc = acc; a.grad_loc = grad_sampling_loc; a.grad_attn = grad_attn_weight;
+        a.N = N; a.S = S; a.M = M; a.D = D; a.L = L; a.Lq = Lq; a.P = P; a.pad_mode = pad_mode;
+        a.assume_1d = one_d ? 1 : 0;
+        a.total = (long long)N * Lq * M * D;
+        rc = launch_generic_bwd<false>(a, dtype, st);
+    }
+    if (rc) return rc;
+    if (dtype == MSDA_BF16) return finish_bf16(static_cast<const float *>(acc), grad_value, nv, st);
+    return MSDA_OK;
+}
+
+int msda_fused_forward(const void *value, const int64_t *temporal_shapes, const int64_t *level_start_index,
+                       const float *reference_points, const float *sampling_offsets, const float *attn_logits,
+                       void *output, int N, int S, int M, int D, int L, int Lq, int P, int R, int dtype, int pad_mode,
+                       unsigned flags, void *stream)
+{
+    (void)flags;
+    g_launches = 0;
+    const Dims d{N, S, M, D, L, Lq, P};
+    if (int e = check_dims(d, dtype, pad_mode)) return e;
+    if (R != 1 && R != 2) return MSDA_ERR_SHAPE;
+    if (!value || !temporal_shapes || !level_start_index || !reference_points || !sampling_offsets || !attn_logits || !output)
+        return MSDA_ERR_NULL;
+    if (!aligned16(value) || !aligned16(output)) return MSDA_ERR_ALIGN;
+    const int lpg = fast_lpg(D, dtype);
+    if (!lpg) return MSDA_ERR_UNSUPPORTED;   // callers fall back to the unfused entry points (still CUDA)
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    FastArgs a{};
+    a.value = value; a.shapes = temporal_shapes; a.lsi = level_start_index; a.shapes_stride = 1;
+    a.ref = reference_points; a.offs = sampling_offsets; a.logits = attn_logits; a.R = R;
+    a.out = output;
+    a.N = N; a.S = S; a.M = M; a.D = D; a.L = L; a.Lq = Lq; a.P = P; a.pad_mode = pad_mode;
+    a.total_units = N * Lq * M;
+    int grid;
+    fast_grid(a.total_units, lpg, grid, a.units_per_cta);
+    return dtype == MSDA_F32 ? launch_fast_fwd<float, true>(a, lpg, grid, st)
+                             : launch_fast_fwd<__nv_bfloat16, true>(a, lpg, grid, st);
+}
+
+int msda_fused_backward(const void *value, const int64_t *temporal_shapes, const int64_t *level_start_index,
+                        const float *reference_points, const float *sampling_offsets, const float *attn_logits,
+                        const void *grad_output, void *grad_value, float *grad_reference_points,
+                        float *grad_sampling_offsets, float *grad_attn_logits, void *workspace, size_t workspace_bytes,
+                        int N, int S, int M, int D, int L, int Lq, int P, int R, int dtype, int pad_mode, unsigned flags,
+                        void *stream)
+{
+    (void)flags;
+    g_launches = 0;
+    const Dims d{N, S, M, D, L, Lq, P};
+    if (int e = check_dims(d, dtype, pad_mode)) return e;
+    if (R != 1 && R != 2) return MSDA_ERR_SHAPE;
+    if (!value || !temporal_shapes || !level_start_index || !reference_points || !sampling_offsets || !attn_logits ||
+        !grad_output || !grad_value || !grad_sampling_offsets || !grad_attn_logits)
+        return MSDA_ERR_NULL;   // grad_reference_points may be NULL (reference points without grad)
+    if (!aligned16(value) || !aligned16(grad_output) || !aligned16(grad_value)) return MSDA_ERR_ALIGN;
+    const int lpg = fast_lpg(D, dtype);
+    if (!lpg) return MSDA_ERR_UNSUPPORTED;
+    const size_t need = msda_backward_workspace_bytes(N, S, M, D, dtype);
+    if (need && (!workspace || workspace_bytes < need || !aligned16(workspace))) return MSDA_ERR_WORKSPACE;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const long long nv = (long long)N * S * M * D;
+    void *acc = dtype == MSDA_BF16 ? workspace : grad_value;
+    if (int e = memset_async(acc, (size_t)nv * 4, st)) return e;
+    if (grad_reference_points)
+        if (int e = memset_async(grad_reference_points, (size_t)N * Lq * L * R * 4, st)) return e;
+    FastArgs a{};
+    a.value = value; a.shapes = temporal_shapes; a.lsi = level_start_index; a.shapes_stride = 1;
+    a.ref = reference_points; a.offs = sampling_offsets; a.logits = attn_logits; a.R = R;
+    a.grad_out = grad_output; a.gv_acc = static_cast<float *>(acc);
+    a.grad_ref = grad_reference_points; a.grad_offs = grad_sampling_offsets; a.grad_logits = grad_attn_logits;
+    a.N = N; a.S = S; a.M = M; a.D = D; a.L = L; a.Lq = Lq; a.P = P; a.pad_mode = pad_mode;
+    a.total_units = N * Lq * M;
+    int grid;
+    fast_grid(a.total_units, lpg, grid, a.units_per_cta);
+    const int rc = dtype == MSDA_F32 ? launch_fast_bwd<float, true>(a, lpg, grid, st)
+                                     : launch_fast_bwd<__nv_bfloat16, true>(a, lpg, grid, st);
+    if (rc) return rc;
+    if (dtype == MSDA_BF16) return finish_bf16(static_cast<const float *>(acc), grad_value, nv, st);
+    return MSDA_OK;
+}
+
+int msda_sample_forward(const void *value, const int64_t *spatial_shapes, const int64_t *level_start_index,
+                        const void *sampling_loc, void *samples, int N, int S, int M, int D, int L, int Lq, int P,
+                        int dtype, int pad_mode, unsigned flags, void *stream)
+{
+    g_launches = 0;
+    const Dims d{N, S, M, D, L, Lq, P};
+    if (int e = check_dims(d, dtype, pad_mode)) return e;
+    if (!value || !spatial_shapes || !level_start_index || !sampling_loc || !samples) return MSDA_ERR_NULL;
+    GenericArgs a{};
+    a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
+    a.loc = sampling_loc; a.out = samples;
+    a.N = N; a.S = S; a.M = M; a.D = D; a.L = L; a.Lq = Lq; a.P = P; a.pad_mode = pad_mode;
+    a.assume_1d = (flags & MSDA_FLAG_ASSUME_1D) ? 1 : 0;
+    a.total = (long long)N * Lq * M * D;
+    return launch_generic_fwd<true>(a, dtype, static_cast<cudaStream_t>(stream));
+}
+
+int msda_sample_backward(const void *value, const int64_t *spatial_shapes, const int64_t *level_start_index,
+                         const void *sampling_loc, const void *grad_samples, void *grad_value, void *grad_sampling_loc,
+                         void *workspace, size_t workspace_bytes, int N, int S, int M, int D, int L, int Lq, int P,
+                         int dtype, int pad_mode, unsigned flags, void *stream)
+{
+    g_launches = 0;
+    const Dims d{N, S, M, D, L, Lq, P};
+    if (int e = check_dims(d, dtype, pad_mode)) return e;
+    if (!value || !spatial_shapes || !level_start_index || !sampling_loc || !grad_samples || !grad_value || !grad_sampling_loc)
+        return MSDA_ERR_NULL;
+    const size_t need = msda_backward_workspace_bytes(N, S, M, D, dtype);
+    if (need && (!workspace || workspace_bytes < need || !aligned16(workspace))) return MSDA_ERR_WORKSPACE;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const long long nv = (long long)N * S * M * D;
+    const long long ns = (long long)N * Lq * M * L * P;
+    const size_t ct = dtype == MSDA_F64 ? 8 : 4;
+    void *acc = dtype == MSDA_BF16 ? workspace : grad_value;
+    if (int e = memset_async(acc, (size_t)nv * ct, st)) return e;
+    if (int e = memset_async(grad_sampling_loc, (size_t)ns * 2 * ct, st)) return e;
+    GenericArgs a{};
+    a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
+    a.loc = sampling_loc; a.grad_out = grad_samples;
+    a.gv_acc = acc; a.grad_loc = grad_sampling_loc;
+    a.N = N; a.S = S; a.M = M; a.D = D; a.L = L; a.Lq = Lq; a.P = P; a.pad_mode = pad_mode;
+    a.assume_1d = (flags & MSDA_FLAG_ASSUME_1D) ? 1 : 0;
+    a.total = (long long)N * Lq * M * D;
+    const int rc = launch_generic_bwd<true>(a, dtype, st);
+    if (rc) return rc;
+    if (dtype == MSDA_BF16) return finish_bf16(static_cast<const float *>(acc), grad_value, nv, st);
+    return MSDA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,322 @@
+"""Autograd functions over the C-ABI CUDA library -- mirror of the reference's
+`pdvc/ops/functions/ms_deform_attn_func.py`.
+
+  MSDeformAttnFunction          same name, argument order and outputs as the reference class
+                                (ms_deform_attn_func.py:20-38); calls msda_ms_deform_attn_forward /
+                                _backward instead of the pybind11 module (func.py:25-26, :34-36).
+  ms_deform_attn_core_pytorch   same signature as the reference helper (func.py:41-68) but executed
+                                by the CUDA library (there is no PyTorch/CPU path in this package).
+  MSDeformAttnFusedFunction     new: softmax + sampling locations + core op in one kernel each way
+                                (replaces ms_deform_attn.py:100-122 for the 1-D temporal case).
+  MSDeformSampleFunction        new: the return_value=True branch (func.py:64-65) as a CUDA op.
+
+Error behaviour follows the reference's host wrapper (ms_deform_attn_cuda.cu:28-38): non-contiguous
+or non-CUDA tensors raise RuntimeError; so do unsupported dtypes.
+"""
+import weakref
+
+import torch
+from torch.autograd import Function
+from torch.autograd.function import once_differentiable
+
+from ... import _lib
+
+_DTYPES = {torch.float32: _lib.F32, torch.bfloat16: _lib.BF16, torch.float64: _lib.F64}
+_PAD = {"border": _lib.PAD_BORDER, "zeros": _lib.PAD_ZEROS}
+_default_padding_mode = "border"
+
+
+def set_default_padding_mode(mode):
+    """'border' (default) = the reference's PyTorch path / parity oracle (func.py:58-59);
+    'zeros' = the reference's CUDA kernel (ms_deform_im2col_cuda.cuh:286-289), for checkpoints trained
+    with that extension."""
+    global _default_padding_mode
+    if mode not in _PAD:
+        raise ValueError(f"padding mode must be 'border' or 'zeros', got {mode!r}")
+    _default_padding_mode = mode
+
+
+def get_default_padding_mode():
+    return _default_padding_mode
+
+
+def _pad_code(mode):
+    mode = _default_padding_mode if mode is None else mode
+    if mode not in _PAD:
+        raise ValueError(f"padding mode must be 'border' or 'zeros', got {mode!r}")
+    return _PAD[mode]
+
+
+def _require(cond, msg):
+    if not cond:
+        raise RuntimeError(msg)
+
+
+def _check_cuda_contig(**tensors):
+    # same wording as AT_ASSERTM in ms_deform_attn_cuda.cu:28-38
+    for name, t in tensors.items():
+        _require(isinstance(t, torch.Tensor), f"{name} must be a tensor")
+        _require(t.is_cuda, f"{name} must be a CUDA tensor")
+        _require(t.is_contiguous(), f"{name} tensor has to be contiguous")
+
+
+def _ptr(t):
+    return t.data_ptr() if t is not None else None
+
+
+def _stream(dev):
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+# spatial_shapes tensors whose H column has already been inspected (one device->host read per tensor)
+_shape_cache = {}
+
+
+def _shapes_are_1d(shapes):
+    """True when every level has H == 1.  Costs one tiny D2H read the first time a given shapes
+    tensor is seen (keyed on tensor identity + version); the nn.Module front-ends never need it
+    because they build the (1, T_l) shapes themselves."""
+    key = id(shapes)
+    hit = _shape_cache.get(key)
+    if hit is not None and hit[0]() is shapes and hit[1] == shapes._version:
+        return hit[2]
+    flag = bool((shapes[:, 0] == 1).all().item())
+    if len(_shape_cache) > 256:
+        _shape_cache.clear()
+    _shape_cache[key] = (weakref.ref(shapes), shapes._version, flag)
+    return flag
+
+
+def _normalise_shapes(shapes):
+    """Accept (L,2) [H,W] (reference layout) or (L,) temporal lengths."""
+    _require(shapes.dtype == torch.int64, "spatial_shapes must be int64")
+    if shapes.dim() == 1:
+        return torch.stack([torch.ones_like(shapes), shapes], -1).contiguous(), True
+    _require(shapes.dim() == 2 and shapes.shape[1] == 2, "spatial_shapes must be (L,2) or (L,)")
+    return shapes, None
+
+
+def _index_dtype_ok(value, *idx_tensors):
+    """loc / attn dtype rule: equal to value's, except bf16 values, which take fp32 (or bf16,
+    up-converted) index-side tensors."""
+    for t in idx_tensors:
+        if value.dtype == torch.bfloat16:
+            _require(t.dtype in (torch.float32, torch.bfloat16), "bf16 value needs fp32/bf16 locations and weights")
+        else:
+            _require(t.dtype == value.dtype, "value, sampling_locations and attention_weights must share a dtype")
+
+
+class MSDeformAttnFunction(Function):
+    """Reference signature: apply(value, value_spatial_shapes, value_level_start_index,
+    sampling_locations, attention_weights, im2col_step) -> (N, Lq, M*D).
+
+    Optional trailing arguments (not in the reference): padding_mode ('border'|'zeros'|None) and
+    assume_1d (True skips the H==1 inspection; the modules pass it)."""
+
+    @staticmethod
+    def forward(ctx, value, value_spatial_shapes, value_level_start_index, sampling_locations,
+                attention_weights, im2col_step=64, padding_mode=None, assume_1d=None, force_generic=False):
+        ctx.n_inputs = 9
+        _check_cuda_contig(value=value, spatial_shapes=value_spatial_shapes,
+                           level_start_index=value_level_start_index, sampling_loc=sampling_locations,
+                           attn_weight=attention_weights)
+        _require(value.dtype in _DTYPES, f"unsupported dtype {value.dtype} (float32, bfloat16, float64)")
+        _require(value.dim() == 4, "value must be (N, S, M, D)")
+        _require(sampling_locations.dim() == 6 and sampling_locations.shape[-1] == 2,
+                 "sampling_locations must be (N, Lq, M, L, P, 2)")
+        _index_dtype_ok(value, sampling_locations, attention_weights)
+        shapes, is1d = _normalise_shapes(value_spatial_shapes)
+        _require(value_level_start_index.dtype == torch.int64, "level_start_index must be int64")
+        N, S, M, D = value.shape
+        _, Lq, M2, L, P, _ = sampling_locations.shape
+        _require(M2 == M and sampling_locations.shape[0] == N, "sampling_locations does not match value")
+        _require(tuple(attention_weights.shape) == (N, Lq, M, L, P), "attention_weights must be (N, Lq, M, L, P)")
+        _require(shapes.shape[0] == L and value_level_start_index.numel() == L, "level tensors do not match L")
+        if assume_1d is None:
+            assume_1d = is1d if is1d is not None else _shapes_are_1d(shapes)
+        loc, attn = sampling_locations, attention_weights
+        if value.dtype == torch.bfloat16:
+            loc, attn = loc.float(), attn.float()
+        flags = (_lib.FLAG_ASSUME_1D if assume_1d else 0) | (_lib.FLAG_FORCE_GENERIC if force_generic else 0)
+        pad = _pad_code(padding_mode)
+        out = torch.empty((N, Lq, M * D), dtype=value.dtype, device=value.device)
+        with torch.cuda.device(value.device):
+            rc = _lib.lib().msda_ms_deform_attn_forward(
+                _ptr(value), _ptr(shapes), _ptr(value_level_start_index), _ptr(loc), _ptr(attn), _ptr(out),
+                N, S, M, D, L, Lq, P, _DTYPES[value.dtype], pad, flags, _stream(value.device))
+        _lib.check(rc, "msda_ms_deform_attn_forward")
+        ctx.im2col_step = im2col_step
+        ctx.pad, ctx.flags = pad, flags
+        ctx.idx_dtypes = (sampling_locations.dtype, attention_weights.dtype)
+        ctx.save_for_backward(value, shapes, value_level_start_index, loc, attn)
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, grad_output):
+        value, shapes, lsi, loc, attn = ctx.saved_tensors
+        N, S, M, D = value.shape
+        _, Lq, _, L, P, _ = loc.shape
+        grad_output = grad_output.contiguous()
+        _require(grad_output.dtype == value.dtype, "grad_output dtype must match value")
+        grad_value = torch.empty_like(value)
+        grad_loc = torch.empty_like(loc)
+        grad_attn = torch.empty_like(attn)
+        lib = _lib.lib()
+        code = _DTYPES[value.dtype]
+        ws_bytes = lib.msda_backward_workspace_bytes(N, S, M, D, code)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=value.device) if ws_bytes else None
+        with torch.cuda.device(value.device):
+            rc = lib.msda_ms_deform_attn_backward(
+                _ptr(value), _ptr(shapes), _ptr(lsi), _ptr(loc), _ptr(attn), _ptr(grad_output),
+                _ptr(grad_value), _ptr(grad_loc), _ptr(grad_attn), _ptr(ws), ws_bytes,
+                N, S, M, D, L, Lq, P, code, ctx.pad, ctx.flags, _stream(value.device))
+        _lib.check(rc, "msda_ms_deform_attn_backward")
+        if grad_loc.dtype != ctx.idx_dtypes[0]:
+            grad_loc = grad_loc.to(ctx.idx_dtypes[0])
+        if grad_attn.dtype != ctx.idx_dtypes[1]:
+            grad_attn = grad_attn.to(ctx.idx_dtypes[1])
+        # (grad_value, None, None, grad_sampling_loc, grad_attn_weight, None) as func.py:38, plus
+        # None for the optional extras
+        return (grad_value, None, None, grad_loc, grad_attn, None, None, None, None)
+
+
+class MSDeformAttnFusedFunction(Function):
+    """apply(value, temporal_shapes, level_start_index, reference_points, sampling_offsets,
+    attn_logits, padding_mode=None) -> (N, Lq, M*D)
+
+    value (N,S,M,D) f32|bf16; temporal_shapes (L,) int64; reference_points (N,Lq,L,1|2) f32;
+    sampling_offsets, attn_logits (N,Lq,M,L,P) f32 -- the raw Linear outputs of the module
+    (ms_deform_attn.py:99-100).  Nothing but the inputs is saved for backward."""
+
+    @staticmethod
+    def forward(ctx, value, temporal_shapes, level_start_index, reference_points, sampling_offsets,
+                attn_logits, padding_mode=None):
+        _check_cuda_contig(value=value, temporal_shapes=temporal_shapes, level_start_index=level_start_index,
+                           reference_points=reference_points, sampling_offsets=sampling_offsets,
+                           attn_logits=attn_logits)
+        _require(value.dtype in (torch.float32, torch.bfloat16), "fused path takes float32 or bfloat16 values")
+        _require(temporal_shapes.dtype == torch.int64 and temporal_shapes.dim() == 1, "temporal_shapes must be (L,) int64")
+        _require(level_start_index.dtype == torch.int64, "level_start_index must be int64")
+        for name, t in (("reference_points", reference_points), ("sampling_offsets", sampling_offsets),
+                        ("attn_logits", attn_logits)):
+            _require(t.dtype == torch.float32, f"{name} must be float32")
+        N, S, M, D = value.shape
+        _require(sampling_offsets.dim() == 5, "sampling_offsets must be (N, Lq, M, L, P)")
+        _, Lq, M2, L, P = sampling_offsets.shape
+        R = reference_points.shape[-1]
+        _require(M2 == M and sampling_offsets.shape[0] == N, "sampling_offsets does not match value")
+        _require(tuple(attn_logits.shape) == (N, Lq, M, L, P), "attn_logits must be (N, Lq, M, L, P)")
+        _require(tuple(reference_points.shape) == (N, Lq, L, R), "reference_points must be (N, Lq, L, R)")
+        if R not in (1, 2):
+            raise ValueError(f"Last dim of reference_points must be 1 or 2, but get {R} instead.")
+        _require(temporal_shapes.numel() == L and level_start_index.numel() == L, "level tensors do not match L")
+        pad = _pad_code(padding_mode)
+        out = torch.empty((N, Lq, M * D), dtype=value.dtype, device=value.device)
+        with torch.cuda.device(value.device):
+            rc = _lib.lib().msda_fused_forward(
+                _ptr(value), _ptr(temporal_shapes), _ptr(level_start_index), _ptr(reference_points),
+                _ptr(sampling_offsets), _ptr(attn_logits), _ptr(out), N, S, M, D, L, Lq, P, R,
+                _DTYPES[value.dtype], pad, 0, _stream(value.device))
+        _lib.check(rc, "msda_fused_forward")
+        ctx.pad = pad
+        ctx.save_for_backward(value, temporal_shapes, level_start_index, reference_points, sampling_offsets,
+                              attn_logits)
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, grad_output):
+        value, shapes, lsi, ref, off, logits = ctx.saved_tensors
+        N, S, M, D = value.shape
+        _, Lq, _, L, P = off.shape
+        R = ref.shape[-1]
+        grad_output = grad_output.contiguous()
+        _require(grad_output.dtype == value.dtype, "grad_output dtype must match value")
+        grad_value = torch.empty_like(value)
+        grad_off = torch.empty_like(off)
+        grad_logits = torch.empty_like(logits)
+        grad_ref = torch.empty_like(ref) if ctx.needs_input_grad[3] else None
+        lib = _lib.lib()
+        code = _DTYPES[value.dtype]
+        ws_bytes = lib.msda_backward_workspace_bytes(N, S, M, D, code)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=value.device) if ws_bytes else None
+        with torch.cuda.device(value.device):
+            rc = lib.msda_fused_backward(
+                _ptr(value), _ptr(shapes), _ptr(lsi), _ptr(ref), _ptr(off), _ptr(logits), _ptr(grad_output),
+                _ptr(grad_value), _ptr(grad_ref), _ptr(grad_off), _ptr(grad_logits), _ptr(ws), ws_bytes,
+                N, S, M, D, L, Lq, P, R, code, ctx.pad, 0, _stream(value.device))
+        _lib.check(rc, "msda_fused_backward")
+        return grad_value, None, None, grad_ref, grad_off, grad_logits, None
+
+
+class MSDeformSampleFunction(Function):
+    """apply(value, spatial_shapes, level_start_index, sampling_locations, padding_mode=None,
+    assume_1d=None) -> un-weighted samples (N*M, D, Lq, L, P)  (func.py:64-65)."""
+
+    @staticmethod
+    def forward(ctx, value, value_spatial_shapes, value_level_start_index, sampling_locations,
+                padding_mode=None, assume_1d=None):
+        _check_cuda_contig(value=value, spatial_shapes=value_spatial_shapes,
+                           level_start_index=value_level_start_index, sampling_loc=sampling_locations)
+        _require(value.dtype in _DTYPES, f"unsupported dtype {value.dtype}")
+        _index_dtype_ok(value, sampling_locations)
+        shapes, is1d = _normalise_shapes(value_spatial_shapes)
+        N, S, M, D = value.shape
+        _, Lq, _, L, P, _ = sampling_locations.shape
+        if assume_1d is None:
+            assume_1d = is1d if is1d is not None else _shapes_are_1d(shapes)
+        loc = sampling_locations.float() if value.dtype == torch.bfloat16 else sampling_locations
+        flags = _lib.FLAG_ASSUME_1D if assume_1d else 0
+        pad = _pad_code(padding_mode)
+        samples = torch.empty((N * M, D, Lq, L, P), dtype=value.dtype, device=value.device)
+        with torch.cuda.device(value.device):
+            rc = _lib.lib().msda_sample_forward(
+                _ptr(value), _ptr(shapes), _ptr(value_level_start_index), _ptr(loc), _ptr(samples),
+                N, S, M, D, L, Lq, P, _DTYPES[value.dtype], pad, flags, _stream(value.device))
+        _lib.check(rc, "msda_sample_forward")
+        ctx.pad, ctx.flags = pad, flags
+        ctx.loc_dtype = sampling_locations.dtype
+        ctx.save_for_backward(value, shapes, value_level_start_index, loc)
+        return samples
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, grad_samples):
+        value, shapes, lsi, loc = ctx.saved_tensors
+        N, S, M, D = value.shape
+        _, Lq, _, L, P, _ = loc.shape
+        grad_samples = grad_samples.contiguous()
+        _require(grad_samples.dtype == value.dtype, "grad_samples dtype must match value")
+        grad_value = torch.empty_like(value)
+        grad_loc = torch.empty_like(loc)
+        lib = _lib.lib()
+        code = _DTYPES[value.dtype]
+        ws_bytes = lib.msda_backward_workspace_bytes(N, S, M, D, code)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=value.device) if ws_bytes else None
+        with torch.cuda.device(value.device):
+            rc = lib.msda_sample_backward(
+                _ptr(value), _ptr(shapes), _ptr(lsi), _ptr(loc), _ptr(grad_samples), _ptr(grad_value),
+                _ptr(grad_loc), _ptr(ws), ws_bytes, N, S, M, D, L, Lq, P, code, ctx.pad, ctx.flags,
+                _stream(value.device))
+        _lib.check(rc, "msda_sample_backward")
+        if grad_loc.dtype != ctx.loc_dtype:
+            grad_loc = grad_loc.to(ctx.loc_dtype)
+        return grad_value, None, None, grad_loc, None, None
+
+
+def ms_deform_attn_core_pytorch(value, value_spatial_shapes, sampling_locations, attention_weights,
+                                return_value=False):
+    """Same call as the reference helper (func.py:41-68): no level_start_index argument, optional
+    return_value.  Executed by the CUDA library; CPU tensors raise RuntimeError (the reference runs
+    F.grid_sample here -- this package ships no CPU path)."""
+    _require(value.is_cuda, "value must be a CUDA tensor (this package has no CPU path)")
+    shapes = torch.as_tensor(value_spatial_shapes, dtype=torch.int64, device=value.device)
+    shapes2, _ = _normalise_shapes(shapes.contiguous())
+    sizes = shapes2[:, 0] * shapes2[:, 1]
+    lsi = torch.cat((sizes.new_zeros((1,)), sizes.cumsum(0)[:-1])).contiguous()
+    value = value.contiguous()
+    loc = sampling_locations.contiguous()
+    if return_value:
+        return MSDeformSampleFunction.apply(value, shapes2, lsi, loc)
+    return MSDeformAttnFunction.apply(value, shapes2, lsi, loc, attention_weights.contiguous(), 64)

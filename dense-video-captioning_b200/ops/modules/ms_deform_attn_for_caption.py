@@ -1,0 +1,28 @@
+"""MSDeformAttnCap -- drop-in for `pdvc/ops/modules/ms_deform_attn_for_caption.py:30-123`.
+
+Same front-end as MSDeformAttn on a 2*d_model query (hidden state + event feature of the caption
+LSTM, pdvc/CaptioningHead/LSTM_DSA.py:239-240); returns the raw sampled values (N*M, D, Lq, L, P) with
+no weighting and no output projection (ms_deform_attn_for_caption.py:120-123).  The reference always
+takes the F.grid_sample path here, even on CUDA; this module runs the sampler CUDA kernel."""
+from ..functions.ms_deform_attn_func import MSDeformSampleFunction
+from .ms_deform_attn import _MSDeformFrontEnd
+
+
+class MSDeformAttnCap(_MSDeformFrontEnd):
+    query_scale = 2
+    centre_offsets = True   # ms_deform_attn_for_caption.py:68
+
+    def __init__(self, d_model=256, n_levels=4, n_heads=8, n_points=4):
+        super().__init__(d_model, n_levels, n_heads, n_points)
+
+    def forward(self, query, reference_points, input_flatten, input_spatial_shapes, input_level_start_index,
+                input_padding_mask=None):
+        value, offsets, logits = self._project(query, reference_points, input_flatten, input_spatial_shapes,
+                                               input_padding_mask)
+        # the attention weights are computed by the reference too (:102-103) but do not reach the output
+        loc, _, shapes2 = self._locations_and_weights(reference_points, offsets, logits, input_spatial_shapes)
+        value = value.contiguous()
+        if value.dtype != loc.dtype and value.dtype.is_floating_point and value.dtype.itemsize >= 4:
+            loc = loc.to(value.dtype)
+        return MSDeformSampleFunction.apply(value, shapes2, input_level_start_index.contiguous(), loc,
+                                            self.padding_mode, True)

@@ -1,0 +1,168 @@
+/*
+ * include/msda.h -- C ABI of libmsda_sm100.so, the B200 (sm_100a) replacement for the reference's
+ * `MultiScaleDeformableAttention` pybind11/ATen extension (pdvc/ops/setup.py:52-61).
+ *
+ * Conventions (all entry points):
+ *   - plain device pointers and sizes; no torch / ATen types.  Every tensor is dense,
+ *     row-major ("contiguous" in the reference's asserts, ms_deform_attn_cuda.cu:28-32) and
+ *     16-byte aligned at its base.
+ *   - the CALLER owns and allocates every buffer (outputs need no pre-zeroing; the library
+ *     zero-fills what it accumulates into).  The library allocates nothing, keeps no pointer
+ *     after return and holds no mutable global state.
+ *   - work is enqueued on `stream` (a cudaStream_t passed as void*; the reference uses
+ *     at::cuda::getCurrentCUDAStream(), ms_deform_attn_cuda.cu:65,:135).  No entry point
+ *     synchronises the host; all are CUDA-graph capturable.
+ *   - return value: 0 on success; > 0 a cudaError_t from the launch (the reference only
+ *     printf()s these, ms_deform_im2col_cuda.cuh:949-953); < 0 an MSDA_ERR_* argument error
+ *     (the reference raises through AT_ASSERTM, ms_deform_attn_cuda.cu:28-52).
+ *     msda_error_string() maps either to text.
+ *   - `spatial_shapes` (L,2) int64 [H_l, W_l] and `level_start_index` (L,) int64 live in DEVICE
+ *     memory exactly as the reference passes them (ms_deform_attn_cuda.cu:66-67) and are read by
+ *     the kernels; no host copy is made.
+ *
+ * dtype: element type of value / output / grad_output / grad_value.
+ *   MSDA_F32 : everything float32.
+ *   MSDA_BF16: value/output/grad_output/grad_value bfloat16; sampling locations, attention
+ *              weights, offsets, logits, reference points and their gradients stay float32;
+ *              accumulation is float32.
+ *   MSDA_F64 : everything float64 (generic kernels only; lets the reference's gradcheck,
+ *              pdvc/ops/test.py:63-78, run against this library).
+ */
+#ifndef MSDA_H_
+#define MSDA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MSDA_VERSION 100 /* 0.1.0 */
+
+enum { MSDA_F32 = 0, MSDA_BF16 = 1, MSDA_F64 = 2 };
+
+/* Out-of-range handling of sampling locations.
+ * BORDER = the reference's PyTorch path (F.grid_sample padding_mode='border',
+ *          pdvc/ops/functions/ms_deform_attn_func.py:58-59) -- the parity oracle.
+ * ZEROS  = the reference's CUDA kernel (ms_deform_im2col_cuda.cuh:286-289, :39-84). */
+enum { MSDA_PAD_BORDER = 0, MSDA_PAD_ZEROS = 1 };
+
+/* flags */
+#define MSDA_FLAG_ASSUME_1D 1u   /* caller guarantees H_l == 1 for every level (PDVC always:
+                                    pdvc/ops/modules/ms_deform_attn.py:114-117); sampling_loc[...,1]
+                                    is ignored and grad_sampling_loc[...,1] is written as 0 */
+#define MSDA_FLAG_FORCE_GENERIC 2u /* testing: take the generic (any-D, 2-D capable) kernels */
+
+enum {
+    MSDA_OK = 0,
+    MSDA_ERR_DTYPE = -1,      /* unknown dtype code / dtype not supported by this entry point */
+    MSDA_ERR_SHAPE = -2,      /* a dimension is <= 0 or exceeds a documented limit */
+    MSDA_ERR_NULL = -3,       /* a required pointer is NULL */
+    MSDA_ERR_ALIGN = -4,      /* a base pointer is not 16-byte aligned */
+    MSDA_ERR_WORKSPACE = -5,  /* workspace smaller than msda_backward_workspace_bytes() */
+    MSDA_ERR_PAD = -6,        /* unknown pad_mode */
+    MSDA_ERR_UNSUPPORTED = -7 /* combination not implemented (e.g. 2-D shapes with bf16 fast path) */
+};
+
+#define MSDA_MAX_LEVELS 32
+
+int msda_version(void);
+/* "sm_100a" -- the only architecture this library contains code for. */
+const char *msda_arch(void);
+const char *msda_error_string(int code);
+
+/* ---------------------------------------------------------------------------------------------
+ * Reference-equivalent entry points.
+ * Replace  ms_deform_attn_forward / ms_deform_attn_backward  exported by the reference module
+ * (pdvc/ops/src/vision.cpp:14-15; signatures pdvc/ops/src/ms_deform_attn.h:20-27, :41-49;
+ * CUDA side pdvc/ops/src/cuda/ms_deform_attn_cuda.cu:20-80, :83-153).
+ *
+ *   value              (N, S, M, D)
+ *   spatial_shapes     (L, 2) int64, device
+ *   level_start_index  (L,)   int64, device
+ *   sampling_loc       (N, Lq, M, L, P, 2)   [...,0] = x along W, [...,1] = y along H
+ *   attn_weight        (N, Lq, M, L, P)
+ *   output             (N, Lq, M*D)
+ * `im2col_step` of the reference has no counterpart: one launch covers any N (a superset of the
+ * reference's `batch % min(batch, im2col_step) == 0` rule, ms_deform_attn_cuda.cu:50-52).
+ * ------------------------------------------------------------------------------------------- */
+int msda_ms_deform_attn_forward(const void *value, const int64_t *spatial_shapes,
+                                const int64_t *level_start_index, const void *sampling_loc,
+                                const void *attn_weight, void *output, int N, int S, int M, int D,
+                                int L, int Lq, int P, int dtype, int pad_mode, unsigned flags,
+                                void *stream);
+
+/* Bytes of scratch msda_ms_deform_attn_backward / msda_fused_backward / msda_sample_backward
+ * need for this problem (0 for f32/f64; an fp32 accumulation image of grad_value for bf16). */
+size_t msda_backward_workspace_bytes(int N, int S, int M, int D, int dtype);
+
+/*   grad_output        (N, Lq, M*D)
+ *   grad_value         (N, S, M, D)           fully overwritten
+ *   grad_sampling_loc  (N, Lq, M, L, P, 2)    fully overwritten
+ *   grad_attn_weight   (N, Lq, M, L, P)       fully overwritten
+ * (the reference allocates these with at::zeros_like, ms_deform_attn_cuda.cu:121-123). */
+int msda_ms_deform_attn_backward(const void *value, const int64_t *spatial_shapes,
+                                 const int64_t *level_start_index, const void *sampling_loc,
+                                 const void *attn_weight, const void *grad_output, void *grad_value,
+                                 void *grad_sampling_loc, void *grad_attn_weight, void *workspace,
+                                 size_t workspace_bytes, int N, int S, int M, int D, int L, int Lq,
+                                 int P, int dtype, int pad_mode, unsigned flags, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Fused 1-D temporal path: replaces, in one kernel each way, the softmax over levels x points,
+ * the sampling-location arithmetic, the dummy-y stacking and the core op of
+ * MSDeformAttn.forward (pdvc/ops/modules/ms_deform_attn.py:100-122).
+ *
+ *   value              (N, S, M, D)          output of value_proj, padding already zeroed
+ *   temporal_shapes    (L,) int64, device    T_l  (the module's input_spatial_shapes, :84)
+ *   level_start_index  (L,) int64, device
+ *   reference_points   (N, Lq, L, R) f32, R in {1, 2}          (:81-82, branches :103-109)
+ *   sampling_offsets   (N, Lq, M, L, P) f32  raw output of the sampling_offsets Linear (:99)
+ *   attn_logits        (N, Lq, M, L, P) f32  raw output of the attention_weights Linear (:100)
+ *   output             (N, Lq, M*D)
+ * Locations: R=1: x = ref0 + off / T_l ; R=2: x = ref0 + off / P * ref1 * 0.5.
+ * Weights:   softmax over the flattened (L*P) axis.
+ * ------------------------------------------------------------------------------------------- */
+int msda_fused_forward(const void *value, const int64_t *temporal_shapes,
+                       const int64_t *level_start_index, const float *reference_points,
+                       const float *sampling_offsets, const float *attn_logits, void *output, int N,
+                       int S, int M, int D, int L, int Lq, int P, int R, int dtype, int pad_mode,
+                       unsigned flags, void *stream);
+
+/*   grad_reference_points (N, Lq, L, R) f32, grad_sampling_offsets / grad_attn_logits
+ *   (N, Lq, M, L, P) f32, grad_value (N, S, M, D); all fully overwritten.  The softmax and the
+ *   locations are recomputed from the raw inputs; nothing is saved by the forward. */
+int msda_fused_backward(const void *value, const int64_t *temporal_shapes,
+                        const int64_t *level_start_index, const float *reference_points,
+                        const float *sampling_offsets, const float *attn_logits,
+                        const void *grad_output, void *grad_value, float *grad_reference_points,
+                        float *grad_sampling_offsets, float *grad_attn_logits, void *workspace,
+                        size_t workspace_bytes, int N, int S, int M, int D, int L, int Lq, int P,
+                        int R, int dtype, int pad_mode, unsigned flags, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Sampler: the return_value=True branch of ms_deform_attn_core_pytorch
+ * (pdvc/ops/functions/ms_deform_attn_func.py:64-65) used by MSDeformAttnCap
+ * (pdvc/ops/modules/ms_deform_attn_for_caption.py:120-121): un-weighted sampled values.
+ *   samples       (N*M, D, Lq, L, P)
+ *   grad_samples  same shape;  grad_value (N,S,M,D), grad_sampling_loc (N,Lq,M,L,P,2) overwritten.
+ * ------------------------------------------------------------------------------------------- */
+int msda_sample_forward(const void *value, const int64_t *spatial_shapes,
+                        const int64_t *level_start_index, const void *sampling_loc, void *samples,
+                        int N, int S, int M, int D, int L, int Lq, int P, int dtype, int pad_mode,
+                        unsigned flags, void *stream);
+
+int msda_sample_backward(const void *value, const int64_t *spatial_shapes,
+                         const int64_t *level_start_index, const void *sampling_loc,
+                         const void *grad_samples, void *grad_value, void *grad_sampling_loc,
+                         void *workspace, size_t workspace_bytes, int N, int S, int M, int D, int L,
+                         int Lq, int P, int dtype, int pad_mode, unsigned flags, void *stream);
+
+/* Number of kernels the last call on this thread launched (bench.py's gpu_launches). */
+int msda_last_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MSDA_H_ */

@@ -1,0 +1,330 @@
+"""GPU parity tests (run on the B200 box with -m gpu): the CUDA library, called through the C ABI by
+the autograd functions, against the CPU oracle (oracle/) on the same seeded inputs and against the
+committed golden vectors produced by the unmodified reference.
+
+Stated tolerances:
+  fp32 kernel vs fp64 oracle on identical (fp32-representable) inputs:  |err| <= 2e-4 * max|ref| + 1e-6
+  bf16 kernel vs fp64 oracle on the bf16-rounded inputs:                |err| <= 1.6e-2 * max|ref| + 1e-6
+  fp64 (generic kernels) vs fp64 oracle:                                |err| <= 1e-10 * max|ref| + 1e-12
+"""
+import numpy as np
+import pytest
+import torch
+
+import cases
+from conftest import load_golden
+from oracle import msda_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+TOL = {torch.float32: (2e-4, 1e-6), torch.bfloat16: (1.6e-2, 1e-6), torch.float64: (1e-10, 1e-12)}
+PAD = {"border": O.BORDER, "zeros": O.ZEROS}
+
+
+@pytest.fixture(scope="module")
+def dvc():
+    import dense_video_captioning_b200 as pkg
+    assert torch.cuda.is_available()
+    return pkg
+
+
+def _round_inputs(inp, dtype):
+    """Round the seeded fp64 inputs to what the kernel will see, so oracle and kernel share bits."""
+    idx_dt = torch.float64 if dtype == torch.float64 else torch.float32
+    out = {}
+    for k in ("value", "grad_out"):
+        out[k] = torch.from_numpy(np.ascontiguousarray(inp[k])).to(dtype)
+    for k in ("loc", "attn"):
+        out[k] = torch.from_numpy(np.ascontiguousarray(inp[k])).to(idx_dt)
+    return out
+
+
+def _np64(t):
+    return t.detach().double().cpu().numpy()
+
+
+def _assert_close(got, want, dtype, what, rel_scale=1.0):
+    rel, ab = TOL[dtype]
+    want = np.asarray(want, dtype=np.float64)
+    got = np.asarray(got, dtype=np.float64)
+    assert got.shape == want.shape, f"{what}: shape {got.shape} vs {want.shape}"
+    scale = np.abs(want).max()
+    err = np.abs(got - want).max()
+    assert np.isfinite(got).all(), f"{what}: non-finite values"
+    assert err <= rel * rel_scale * scale + ab, f"{what}: max|err| {err:.3e} > {rel * rel_scale:.1e} * {scale:.3e}"
+
+
+def _run_core(dvc, t, shapes, pad, **kw):
+    dev = "cuda"
+    value = t["value"].to(dev).requires_grad_(True)
+    loc = t["loc"].to(dev).requires_grad_(True)
+    attn = t["attn"].to(dev).requires_grad_(True)
+    shp = torch.from_numpy(shapes).to(dev)
+    lsi = torch.from_numpy(cases.level_start_index(shapes)).to(dev)
+    out = dvc.MSDeformAttnFunction.apply(value, shp, lsi, loc, attn, 64, pad, *kw.get("extra", ()))
+    out.backward(t["grad_out"].to(dev))
+    torch.cuda.synchronize()
+    return out, value.grad, loc.grad, attn.grad
+
+
+def _oracle(t, shapes, pad):
+    v, l, a, g = (_np64(t[k]) for k in ("value", "loc", "attn", "grad_out"))
+    out = O.forward(v, shapes, l, a, PAD[pad])
+    gv, gl, ga = O.backward(v, shapes, l, a, g, PAD[pad])
+    return out, gv, gl, ga
+
+
+ONE_D = [c for c in cases.ALL_CORE_CASES if c not in ("ref_test_2d", "ragged_2d", "vec_2d")]
+
+
+@pytest.mark.parametrize("pad", ["border", "zeros"])
+@pytest.mark.parametrize("name", ONE_D)
+def test_core_fp32_vs_oracle(dvc, name, pad):
+    inp = cases.core_inputs(name)
+    t = _round_inputs(inp, torch.float32)
+    got = _run_core(dvc, t, inp["shapes"], pad)
+    want = _oracle(t, inp["shapes"], pad)
+    for g, w, what in zip(got, want, ("out", "grad_value", "grad_loc", "grad_attn")):
+        _assert_close(_np64(g), w, torch.float32, f"{name}/{pad}/{what}")
+    assert float(got[2][..., 1].abs().max()) == 0.0   # dummy-y gradient is exactly 0
+
+
+@pytest.mark.parametrize("name", ["yc2_dec", "anet_enc", "p8_d32", "edges", "wide_range", "p16_d128_l1"])
+def test_core_fp32_generic_kernels_vs_oracle(dvc, name):
+    """Same problems through the shape-generic kernels (MSDA_FLAG_FORCE_GENERIC)."""
+    inp = cases.core_inputs(name)
+    t = _round_inputs(inp, torch.float32)
+    got = _run_core(dvc, t, inp["shapes"], "border", extra=(None, True))
+    want = _oracle(t, inp["shapes"], "border")
+    for g, w, what in zip(got, want, ("out", "grad_value", "grad_loc", "grad_attn")):
+        _assert_close(_np64(g), w, torch.float32, f"{name}/generic/{what}")
+
+
+@pytest.mark.parametrize("pad", ["border", "zeros"])
+@pytest.mark.parametrize("name", ["ref_test_2d", "ragged_2d", "vec_2d", "odd_d71"])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_core_2d_and_fp64_vs_oracle(dvc, name, pad, dtype):
+    """True 2-D levels and fp64 (what pdvc/ops/test.py exercises) run on the generic kernels."""
+    inp = cases.core_inputs(name)
+    t = _round_inputs(inp, dtype)
+    got = _run_core(dvc, t, inp["shapes"], pad)
+    want = _oracle(t, inp["shapes"], pad)
+    for g, w, what in zip(got, want, ("out", "grad_value", "grad_loc", "grad_attn")):
+        _assert_close(_np64(g), w, dtype, f"{name}/{pad}/{what}")
+
+
+@pytest.mark.parametrize("pad", ["border", "zeros"])
+@pytest.mark.parametrize("name", ["yc2_dec", "anet_enc", "p8_d32", "p16_d128_l1", "edges", "uniform01"])
+def test_core_bf16_vs_oracle(dvc, name, pad):
+    inp = cases.core_inputs(name)
+    if inp["value"].shape[-1] % 8:
+        pytest.skip("bf16 vector path needs D % 8 == 0")
+    t = _round_inputs(inp, torch.bfloat16)
+    got = _run_core(dvc, t, inp["shapes"], pad)
+    want = _oracle(t, inp["shapes"], pad)
+    for g, w, what in zip(got, want, ("out", "grad_value", "grad_loc", "grad_attn")):
+        _assert_close(_np64(g), w, torch.bfloat16, f"{name}/{pad}/bf16/{what}")
+
+
+@pytest.mark.parametrize("name", ["yc2_dec", "anet_enc", "edges", "cap_m1_d512", "uniform01"])
+def test_core_fp32_vs_reference_golden(dvc, name):
+    """Directly against the numbers the unmodified reference produced (tests/golden)."""
+    inp = cases.core_inputs(name)
+    g = load_golden("core_border_" + name)
+    t = _round_inputs(inp, torch.float32)
+    got = _run_core(dvc, t, inp["shapes"], "border")
+    # the golden run used the un-rounded fp64 inputs: allow the input-rounding error on top
+    for arr, key in zip(got, ("out", "grad_value", "grad_loc", "grad_attn")):
+        _assert_close(_np64(arr), g[key], torch.float32, f"{name}/golden/{key}", rel_scale=4.0)
+
+
+def test_zeros_mode_vs_reference_golden(dvc):
+    inp = cases.core_inputs("yc2_dec")
+    g = load_golden("core_zeros_yc2_dec")
+    t = _round_inputs(inp, torch.float32)
+    got = _run_core(dvc, t, inp["shapes"], "zeros")
+    for arr, key in zip(got, ("out", "grad_value", "grad_loc", "grad_attn")):
+        _assert_close(_np64(arr), g[key], torch.float32, f"zeros/golden/{key}", rel_scale=4.0)
+
+
+# ------------------------------------------------------------------------------------------------
+# fused front-end
+# ------------------------------------------------------------------------------------------------
+def _fused_inputs(seed, N, M, D, T, Lq, P, R):
+    rs = np.random.RandomState(seed)
+    L = len(T)
+    S = sum(T)
+    value = rs.standard_normal((N, S, M, D))
+    if R == 1:
+        ref = rs.uniform(0.0, 1.0, (N, Lq, L, 1))
+    else:
+        ref = np.stack([rs.uniform(0.05, 0.95, (N, Lq, L)), rs.uniform(0.02, 0.5, (N, Lq, L))], -1)
+    off = rs.standard_normal((N, Lq, M, L, P)) * 2.5
+    logits = rs.standard_normal((N, Lq, M, L, P)) * 1.5
+    grad_out = rs.standard_normal((N, Lq, M * D))
+    return dict(value=value, ref=ref, off=off, logits=logits, grad_out=grad_out, T=np.asarray(T, dtype=np.int64))
+
+
+def _nudge_off_knots(inp, P):
+    """Shift offsets so that no sample sits within 2e-4 px of an interpolation knot."""
+    x = O.sampling_locations(inp["ref"].astype(np.float32).astype(np.float64),
+                             inp["off"].astype(np.float32).astype(np.float64), inp["T"], P)
+    T = inp["T"].astype(np.float64)[None, None, None, :, None]
+    pix = x * T - 0.5
+    frac = pix - np.floor(pix)
+    bad = (frac < 5e-4) | (frac > 1 - 5e-4)
+    inp["off"] = np.where(bad, inp["off"] + 0.0137, inp["off"])
+    return inp
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("pad", ["border", "zeros"])
+@pytest.mark.parametrize("cfg", [
+    dict(seed=21, N=1, M=8, D=64, T=cases.level_lengths(200), Lq=100, P=4, R=1),
+    dict(seed=22, N=2, M=8, D=64, T=cases.level_lengths(100), Lq=188, P=4, R=2),
+    dict(seed=23, N=1, M=4, D=32, T=cases.level_lengths(40), Lq=19, P=8, R=1),
+    dict(seed=24, N=1, M=2, D=128, T=[30, 15], Lq=9, P=16, R=2),
+    dict(seed=25, N=2, M=3, D=16, T=[12], Lq=5, P=3, R=1),
+])
+def test_fused_vs_oracle(dvc, cfg, pad, dtype):
+    if dtype == torch.bfloat16 and cfg["D"] < 32:
+        pytest.skip("bf16 vector path needs D >= 32")
+    inp = _nudge_off_knots(_fused_inputs(**cfg), cfg["P"])
+    dev = "cuda"
+    value = torch.from_numpy(inp["value"]).to(dtype).to(dev).requires_grad_(True)
+    ref = torch.from_numpy(inp["ref"]).float().to(dev).requires_grad_(True)
+    off = torch.from_numpy(inp["off"]).float().to(dev).requires_grad_(True)
+    logits = torch.from_numpy(inp["logits"]).float().to(dev).requires_grad_(True)
+    gout = torch.from_numpy(inp["grad_out"]).to(dtype).to(dev)
+    T = torch.from_numpy(inp["T"]).to(dev)
+    lsi = torch.from_numpy(cases.level_start_index(cases.as_shapes2(inp["T"]))).to(dev)
+    out = dvc.MSDeformAttnFusedFunction.apply(value, T, lsi, ref, off, logits, pad)
+    out.backward(gout)
+    torch.cuda.synchronize()
+    v64, r64, o64, l64, g64 = (_np64(x) for x in (value, ref, off, logits, gout))
+    want_out = O.fused_forward(v64, inp["T"], r64, o64, l64, PAD[pad])
+    gv, g_ref, g_off, g_logits = O.fused_backward(v64, inp["T"], r64, o64, l64, g64, PAD[pad])
+    _assert_close(_np64(out), want_out, dtype, "fused/out")
+    _assert_close(_np64(value.grad), gv, dtype, "fused/grad_value")
+    _assert_close(_np64(off.grad), g_off, dtype, "fused/grad_offsets")
+    _assert_close(_np64(logits.grad), g_logits, dtype, "fused/grad_logits")
+    _assert_close(_np64(ref.grad), g_ref, dtype, "fused/grad_ref")
+
+
+# ------------------------------------------------------------------------------------------------
+# sampler (return_value=True branch)
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["cap_m1_d512", "edges", "p8_d32"])
+def test_sampler_vs_reference_golden(dvc, name):
+    inp = cases.core_inputs(name)
+    g = load_golden("core_border_" + name)
+    dev = "cuda"
+    value = torch.from_numpy(inp["value"]).float().to(dev).requires_grad_(True)
+    loc = torch.from_numpy(inp["loc"]).float().to(dev).requires_grad_(True)
+    shp = torch.from_numpy(inp["shapes"]).to(dev)
+    lsi = torch.from_numpy(inp["lsi"]).to(dev)
+    samples = dvc.MSDeformSampleFunction.apply(value, shp, lsi, loc)
+    gs = np.random.RandomState(1234).standard_normal(tuple(samples.shape))
+    samples.backward(torch.from_numpy(gs).float().to(dev))
+    torch.cuda.synchronize()
+    _assert_close(_np64(samples), g["samples"], torch.float32, "samples", rel_scale=4.0)
+    _assert_close(_np64(value.grad), g["sgrad_value"], torch.float32, "sgrad_value", rel_scale=4.0)
+    _assert_close(_np64(loc.grad), g["sgrad_loc"], torch.float32, "sgrad_loc", rel_scale=4.0)
+
+
+# ------------------------------------------------------------------------------------------------
+# module drop-in: reference state_dict -> new module, output and gradients vs the reference's
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("tag", ["attn_ref1_nomask", "attn_ref1_mask", "attn_ref2_nomask", "attn_ref2_mask",
+                                 "cap_ref1_nomask", "cap_ref1_mask", "cap_ref2_nomask", "cap_ref2_mask"])
+def test_module_dropin_vs_reference_golden(dvc, tag):
+    g = load_golden("module_" + tag)
+    cls = dvc.MSDeformAttnCap if tag.startswith("cap") else dvc.MSDeformAttn
+    m = cls(int(g["d_model"]), int(g["n_levels"]), int(g["n_heads"]), int(g["n_points"]))
+    sd = {k[len("param."):]: torch.from_numpy(v).float() for k, v in g.items() if k.startswith("param.")}
+    m.load_state_dict(sd, strict=True)
+    m = m.cuda()
+    dev = "cuda"
+    query = torch.from_numpy(g["query"]).float().to(dev).requires_grad_(True)
+    src = torch.from_numpy(g["src"]).float().to(dev).requires_grad_(True)
+    ref = torch.from_numpy(g["ref"]).float().to(dev).requires_grad_(True)
+    T = torch.from_numpy(g["T"]).to(dev)
+    lsi = torch.cat((T.new_zeros((1,)), T.cumsum(0)[:-1]))
+    mask = torch.from_numpy(g["mask"]).to(dev) if g["mask"].size else None
+    out = m(query, ref, src, T, lsi, mask)
+    out.backward(torch.from_numpy(g["grad_out"]).float().to(dev))
+    torch.cuda.synchronize()
+    _assert_close(_np64(out), g["out"], torch.float32, tag + "/out", rel_scale=4.0)
+    _assert_close(_np64(query.grad), g["grad_query"], torch.float32, tag + "/grad_query", rel_scale=4.0)
+    _assert_close(_np64(src.grad), g["grad_src"], torch.float32, tag + "/grad_src", rel_scale=4.0)
+    _assert_close(_np64(ref.grad), g["grad_ref"], torch.float32, tag + "/grad_ref", rel_scale=4.0)
+    for name, p in m.named_parameters():
+        want = g["gparam." + name]
+        if p.grad is None:
+            assert np.abs(want).max() == 0.0, f"{tag}: missing grad for {name}"
+            continue
+        _assert_close(_np64(p.grad), want, torch.float32, f"{tag}/grad {name}", rel_scale=4.0)
+
+
+# ------------------------------------------------------------------------------------------------
+# API contract (ms_deform_attn_cuda.cu:28-52)
+# ------------------------------------------------------------------------------------------------
+def test_api_contract_errors(dvc):
+    inp = cases.core_inputs("p8_d32")
+    t = _round_inputs(inp, torch.float32)
+    dev = "cuda"
+    shp = torch.from_numpy(inp["shapes"]).to(dev)
+    lsi = torch.from_numpy(inp["lsi"]).to(dev)
+    v, l, a = t["value"].to(dev), t["loc"].to(dev), t["attn"].to(dev)
+    with pytest.raises(RuntimeError, match="contiguous"):
+        dvc.MSDeformAttnFunction.apply(v.transpose(1, 2).contiguous().transpose(1, 2), shp, lsi, l, a, 64)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        dvc.MSDeformAttnFunction.apply(v.cpu(), shp, lsi, l, a, 64)
+    with pytest.raises(RuntimeError, match="dtype"):
+        dvc.MSDeformAttnFunction.apply(v.half(), shp, lsi, l.half(), a.half(), 64)
+    with pytest.raises(RuntimeError, match="dtype"):
+        dvc.MSDeformAttnFunction.apply(v, shp, lsi, l.double(), a, 64)
+    with pytest.raises(RuntimeError):
+        dvc.ms_deform_attn_core_pytorch(v.cpu(), inp["shapes"], l.cpu(), a.cpu())
+    m = dvc.MSDeformAttn(64, 4, 4, 4)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        m(torch.zeros(1, 3, 64), torch.zeros(1, 3, 4, 1), torch.zeros(1, 15, 64),
+          torch.tensor([8, 4, 2, 1]), torch.tensor([0, 8, 12, 14]))
+
+
+@pytest.mark.parametrize("N", [65, 130])
+def test_batch_not_multiple_of_im2col_step(dvc, N):
+    """The reference asserts batch % min(batch, 64) == 0 (ms_deform_attn_cuda.cu:50-52); one launch here
+    covers any N -- check every sample against the oracle of sample 0 replicated."""
+    base = cases.make_core_inputs(seed=31, N=1, M=2, D=32, shapes=cases.level_lengths(16), Lq=5, P=4)
+    t = _round_inputs(base, torch.float32)
+    rep = {k: v.repeat(N, *([1] * (v.dim() - 1))).contiguous() for k, v in t.items()}
+    got = _run_core(dvc, rep, base["shapes"], "border")
+    want = _oracle(t, base["shapes"], "border")
+    for g, w, what in zip(got, want, ("out", "grad_value", "grad_loc", "grad_attn")):
+        g = _np64(g)
+        _assert_close(g[:1], w, torch.float32, f"N={N}/{what}[0]")
+        _assert_close(g[-1:], w, torch.float32, f"N={N}/{what}[-1]")
+
+
+def test_core_pytorch_name_runs_on_cuda(dvc):
+    """ms_deform_attn_core_pytorch keeps its reference signature but is CUDA-backed."""
+    inp = cases.core_inputs("p8_d32")
+    t = _round_inputs(inp, torch.float32)
+    out = dvc.ms_deform_attn_core_pytorch(t["value"].cuda(), inp["shapes"], t["loc"].cuda(), t["attn"].cuda())
+    want = O.forward(_np64(t["value"]), inp["shapes"], _np64(t["loc"]), _np64(t["attn"]))
+    _assert_close(_np64(out), want, torch.float32, "core_pytorch/out")
+    samples = dvc.ms_deform_attn_core_pytorch(t["value"].cuda(), inp["shapes"], t["loc"].cuda(), t["attn"].cuda(),
+                                              return_value=True)
+    _, want_s = O.forward(_np64(t["value"]), inp["shapes"], _np64(t["loc"]), _np64(t["attn"]), return_samples=True)
+    _assert_close(_np64(samples), want_s, torch.float32, "core_pytorch/samples")
+
+
+def test_backward_run_to_run_variation_is_bounded(dvc):
+    """grad_value uses fp32 atomics (like the reference, ms_deform_im2col_cuda.cuh:126-153): summation
+    order may vary, the result may not by more than rounding."""
+    inp = cases.core_inputs("anet_enc")
+    t = _round_inputs(inp, torch.float32)
+    a = _np64(_run_core(dvc, t, inp["shapes"], "border")[1])
+    b = _np64(_run_core(dvc, t, inp["shapes"], "border")[1])
+    assert np.abs(a - b).max() <= 1e-5 * np.abs(a).max()
