@@ -31,8 +31,9 @@ def _common(value, spatial_shapes, level_start_index, sampling_loc, attn_weight)
     _f._require(sampling_loc.dtype == value.dtype and attn_weight.dtype == value.dtype, "dtype mismatch")
     N, S, M, D = value.shape
     _, Lq, _, L, P, _ = sampling_loc.shape
-    flags = _lib.FLAG_ASSUME_1D if _f._shapes_are_1d(spatial_shapes) else 0
-    return N, S, M, D, L, Lq, P, _f._DTYPES[value.dtype], _f._pad_code(None), flags
+    pad = _f._pad_code(None)
+    flags = _lib.FLAG_ASSUME_1D if _f._auto_1d(spatial_shapes, None, sampling_loc, pad) else 0
+    return N, S, M, D, L, Lq, P, _f._DTYPES[value.dtype], pad, flags
 
 
 def ms_deform_attn_forward(value, spatial_shapes, level_start_index, sampling_loc, attn_weight, im2col_step):

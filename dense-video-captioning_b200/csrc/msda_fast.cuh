@@ -339,7 +339,10 @@ __global__ void __launch_bounds__(kFastThreads) msda_bwd_fast_kernel(const FastA
             if (!FUSED) {
                 if (own_on) {
                     a.grad_attn[sidx] = ga;
-                    *reinterpret_cast<float2 *>(a.grad_loc + 2 * sidx) = make_float2(gx, 0.f);
+                    // dummy y (= 0.5 on an H = 1 level): BORDER clamps it, gradient exactly 0; ZEROS keeps
+                    // the row-0 weight 1 - |y*H - 0.5| whose slope the reference kernel reports (cuh:159)
+                    const float gy = a.pad_mode == MSDA_PAD_ZEROS ? -own.A * ga : 0.f;
+                    *reinterpret_cast<float2 *>(a.grad_loc + 2 * sidx) = make_float2(gx, gy);
                 }
             } else {
                 if (own_on) {

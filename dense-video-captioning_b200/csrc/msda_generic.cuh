@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(256) msda_fwd_generic_kernel(const GenericArgs
                 const long long sidx = u * LP + l * a.P + p;
                 const AxisTap<CT> tx = locate_axis<CT>(loc[2 * sidx], W, a.pad_mode);
                 AxisTap<CT> ty;
-                if (a.assume_1d) { ty.i0 = ty.i1 = 0; ty.w0 = (CT)1; ty.w1 = (CT)0; ty.s0 = ty.s1 = (CT)0; }
+                if (a.assume_1d) { ty.i0 = ty.i1 = 0; ty.w0 = (CT)1; ty.w1 = (CT)0; ty.s0 = a.pad_mode == MSDA_PAD_ZEROS ? (CT)-1 : (CT)0; ty.s1 = (CT)0; }
                 else ty = locate_axis<CT>(loc[2 * sidx + 1], H, a.pad_mode);
                 CT sv = (CT)0;
                 if (ty.w0 != (CT)0) {
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(256) msda_bwd_generic_kernel(const GenericArgs
                 const long long sidx = u * LP + l * a.P + p;
                 const AxisTap<CT> tx = locate_axis<CT>(loc[2 * sidx], W, a.pad_mode);
                 AxisTap<CT> ty;
-                if (a.assume_1d) { ty.i0 = ty.i1 = 0; ty.w0 = (CT)1; ty.w1 = (CT)0; ty.s0 = ty.s1 = (CT)0; }
+                if (a.assume_1d) { ty.i0 = ty.i1 = 0; ty.w0 = (CT)1; ty.w1 = (CT)0; ty.s0 = a.pad_mode == MSDA_PAD_ZEROS ? (CT)-1 : (CT)0; ty.s1 = (CT)0; }
                 else ty = locate_axis<CT>(loc[2 * sidx + 1], H, a.pad_mode);
                 CT gs;   // gradient reaching this sample's interpolated value, for channel d
                 if (SAMPLER) gs = (CT)to_ct(grad_out[(((n * a.M + m) * a.D + d) * a.Lq + q) * LP + l * a.P + p]);

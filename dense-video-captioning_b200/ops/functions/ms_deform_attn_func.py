@@ -87,6 +87,17 @@ def _shapes_are_1d(shapes):
     return flag
 
 
+def _auto_1d(shapes, is1d, loc, pad):
+    """Decide whether the 1-D temporal kernels may take a call whose caller did not say.
+    H == 1 everywhere is enough under BORDER (the clamped y has no effect at all); under ZEROS the
+    row weight depends on y, so the dummy y = 0.5 of ms_deform_attn.py:114-115 is verified too
+    (one more tiny D2H read -- the nn.Modules pass assume_1d=True and never get here)."""
+    flat = is1d if is1d is not None else _shapes_are_1d(shapes)
+    if flat and pad == _lib.PAD_ZEROS:
+        flat = bool((loc[..., 1] == 0.5).all().item())
+    return flat
+
+
 def _normalise_shapes(shapes):
     """Accept (L,2) [H,W] (reference layout) or (L,) temporal lengths."""
     _require(shapes.dtype == torch.int64, "spatial_shapes must be int64")
@@ -132,13 +143,13 @@ class MSDeformAttnFunction(Function):
         _require(M2 == M and sampling_locations.shape[0] == N, "sampling_locations does not match value")
         _require(tuple(attention_weights.shape) == (N, Lq, M, L, P), "attention_weights must be (N, Lq, M, L, P)")
         _require(shapes.shape[0] == L and value_level_start_index.numel() == L, "level tensors do not match L")
+        pad = _pad_code(padding_mode)
         if assume_1d is None:
-            assume_1d = is1d if is1d is not None else _shapes_are_1d(shapes)
+            assume_1d = _auto_1d(shapes, is1d, sampling_locations, pad)
         loc, attn = sampling_locations, attention_weights
         if value.dtype == torch.bfloat16:
             loc, attn = loc.float(), attn.float()
         flags = (_lib.FLAG_ASSUME_1D if assume_1d else 0) | (_lib.FLAG_FORCE_GENERIC if force_generic else 0)
-        pad = _pad_code(padding_mode)
         out = torch.empty((N, Lq, M * D), dtype=value.dtype, device=value.device)
         with torch.cuda.device(value.device):
             rc = _lib.lib().msda_ms_deform_attn_forward(
@@ -264,11 +275,11 @@ class MSDeformSampleFunction(Function):
         shapes, is1d = _normalise_shapes(value_spatial_shapes)
         N, S, M, D = value.shape
         _, Lq, _, L, P, _ = sampling_locations.shape
+        pad = _pad_code(padding_mode)
         if assume_1d is None:
-            assume_1d = is1d if is1d is not None else _shapes_are_1d(shapes)
+            assume_1d = _auto_1d(shapes, is1d, sampling_locations, pad)
         loc = sampling_locations.float() if value.dtype == torch.bfloat16 else sampling_locations
         flags = _lib.FLAG_ASSUME_1D if assume_1d else 0
-        pad = _pad_code(padding_mode)
         samples = torch.empty((N * M, D, Lq, L, P), dtype=value.dtype, device=value.device)
         with torch.cuda.device(value.device):
             rc = _lib.lib().msda_sample_forward(

@@ -49,9 +49,11 @@ enum { MSDA_F32 = 0, MSDA_BF16 = 1, MSDA_F64 = 2 };
 enum { MSDA_PAD_BORDER = 0, MSDA_PAD_ZEROS = 1 };
 
 /* flags */
-#define MSDA_FLAG_ASSUME_1D 1u   /* caller guarantees H_l == 1 for every level (PDVC always:
-                                    pdvc/ops/modules/ms_deform_attn.py:114-117); sampling_loc[...,1]
-                                    is ignored and grad_sampling_loc[...,1] is written as 0 */
+#define MSDA_FLAG_ASSUME_1D 1u   /* caller guarantees H_l == 1 and sampling_loc[...,1] == 0.5 for every
+                                    sample (PDVC always: pdvc/ops/modules/ms_deform_attn.py:114-117).
+                                    sampling_loc[...,1] is not read; grad_sampling_loc[...,1] is what the
+                                    reference computes for y = 0.5: exactly 0 under BORDER, and
+                                    -attn * grad_attn under ZEROS (ms_deform_im2col_cuda.cuh:159) */
 #define MSDA_FLAG_FORCE_GENERIC 2u /* testing: take the generic (any-D, 2-D capable) kernels */
 
 enum {

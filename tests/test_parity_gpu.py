@@ -86,7 +86,8 @@ def test_core_fp32_vs_oracle(dvc, name, pad):
     want = _oracle(t, inp["shapes"], pad)
     for g, w, what in zip(got, want, ("out", "grad_value", "grad_loc", "grad_attn")):
         _assert_close(_np64(g), w, torch.float32, f"{name}/{pad}/{what}")
-    assert float(got[2][..., 1].abs().max()) == 0.0   # dummy-y gradient is exactly 0
+    if pad == "border":
+        assert float(got[2][..., 1].abs().max()) == 0.0   # dummy-y gradient is exactly 0
 
 
 @pytest.mark.parametrize("name", ["yc2_dec", "anet_enc", "p8_d32", "edges", "wide_range", "p16_d128_l1"])
