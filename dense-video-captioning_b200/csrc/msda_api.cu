@@ -6,9 +6,11 @@
 // (cu:61-75) and no silent printf on launch failure (ms_deform_im2col_cuda.cuh:949-953): errors come
 // back as return codes.
 #include <cstdio>
+#include <cstdlib>
 
 #include "msda_fast.cuh"
 #include "msda_generic.cuh"
+#include "msda_tile.cuh"
 
 using namespace msda;
 
@@ -17,6 +19,12 @@ namespace {
 thread_local int g_launches = 0;
 
 constexpr int kNumSMs = 148;   // B200; grids are sized in multiples of it
+
+inline int head_major_env()
+{
+    static const int v = [] { const char *e = getenv("MSDA_HEAD_MAJOR"); return e ? atoi(e) : 1; }();
+    return v;
+}
 
 inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
@@ -92,6 +100,131 @@ template <typename VT, bool FUSED> int launch_fast_bwd(const FastArgs &a, int lp
         default: msda_bwd_fast_kernel<VT, 32, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
     }
     return check_launch();
+}
+
+// ---- chunked ("tile") kernels: planning ----------------------------------------------------------
+
+inline int env_int(const char *name, int dflt)
+{
+    const char *e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+
+struct TilePlan {
+    bool ok;
+    int lpg, lpa, Q, chunks, LPpad, win_rows;
+    size_t smem;
+};
+
+constexpr size_t kMaxDynSmem = 227 * 1024 - 2048;   // opt-in limit minus the kernels' static shared memory
+
+// lanes per value row (16 bytes each): the tile kernels need a power of two between 4 and 32
+int tile_lpg(int D, int dtype)
+{
+    const int ch = dtype == MSDA_BF16 ? 8 : 4;
+    if (dtype == MSDA_F64 || D % ch != 0) return 0;
+    const int lanes = D / ch;
+    return (lanes == 4 || lanes == 8 || lanes == 16 || lanes == 32) ? lanes : 0;
+}
+
+TilePlan tile_plan(const Dims &d, int dtype, bool backward)
+{
+    static const int use_tile = env_int("MSDA_TILE", 1);
+    static const int q_env = env_int("MSDA_Q", 0);
+    static const int win_kb = env_int("MSDA_WIN_KB", 64);
+    TilePlan p{};
+    p.lpg = tile_lpg(d.D, dtype);
+    if (!use_tile || !p.lpg) return p;
+    const int LP = d.L * d.P;
+    p.LPpad = (LP + 3) / 4 * 4;
+    if (p.LPpad > 256) return p;
+    p.lpa = LP <= 16 ? 16 : 32;
+    int Q = 1024 / p.LPpad;
+    Q = Q > 64 ? 64 : (Q < 4 ? 4 : Q);
+    // small problems: more, smaller chunks so that every SM gets a CTA
+    while (Q > 8 && (long long)d.N * d.M * ((d.Lq + Q - 1) / Q) < 2 * kNumSMs) Q >>= 1;
+    if (q_env > 0) Q = q_env;
+    if (Q > d.Lq) Q = d.Lq;
+    if (Q * p.LPpad > kTileMaxSamples) return p;
+    p.Q = Q;
+    p.chunks = (d.Lq + Q - 1) / Q;
+    if ((long long)d.N * d.M * p.chunks >= (1ll << 31)) return p;
+    const int rb = d.D * (dtype == MSDA_BF16 ? 2 : 4);
+    if (backward) {
+        p.smem = bwd_tile_smem_bytes(Q, p.LPpad, d.S, rb);
+        if (p.smem > kMaxDynSmem || d.S >= (1 << kRecLevelShift)) return p;
+    } else {
+        const size_t recs = (size_t)Q * p.LPpad * sizeof(int4);
+        size_t win = (size_t)win_kb * 1024;
+        if (recs + win > kMaxDynSmem) win = kMaxDynSmem > recs ? kMaxDynSmem - recs : 0;
+        p.win_rows = (int)(win / rb);
+        if (p.win_rows > d.S) p.win_rows = d.S;   // the whole head slice fits
+        p.smem = recs + (size_t)p.win_rows * rb;
+        if (p.smem > kMaxDynSmem || d.S >= (1 << kRecLevelShift)) return p;
+    }
+    p.ok = true;
+    return p;
+}
+
+void fill_tile_args(TileArgs &a, const Dims &d, const TilePlan &p, int pad_mode)
+{
+    a.N = d.N; a.S = d.S; a.M = d.M; a.D = d.D; a.L = d.L; a.Lq = d.Lq; a.P = d.P;
+    a.pad_mode = pad_mode;
+    a.LP = d.L * d.P;
+    a.LPpad = p.LPpad;
+    a.invP = 1.f / (float)d.P;
+    a.Q = p.Q;
+    a.chunks = p.chunks;
+    a.win_rows = p.win_rows;
+}
+
+// opt in to > 48 KB of dynamic shared memory once per kernel instantiation and device
+template <typename K> int allow_big_smem(K kernel, unsigned long long &done_mask)
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev > 63) dev = 63, done_mask &= ~(1ull << 63);
+    if (done_mask & (1ull << dev)) return 0;
+    const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+    if (e != cudaSuccess) return (int)e;
+    done_mask |= 1ull << dev;
+    return 0;
+}
+
+template <typename VT, int LPG, int LPA, bool FUSED, bool BWD>
+int launch_tile_inst(const TileArgs &a, int grid, size_t smem, cudaStream_t st)
+{
+    static unsigned long long done = 0;
+    if (BWD) {
+        if (int e = allow_big_smem(msda_bwd_tile_kernel<VT, LPG, LPA, FUSED>, done)) return e;
+        msda_bwd_tile_kernel<VT, LPG, LPA, FUSED><<<grid, kTileThreads, smem, st>>>(a);
+    } else {
+        if (int e = allow_big_smem(msda_fwd_tile_kernel<VT, LPG, LPA, FUSED>, done)) return e;
+        msda_fwd_tile_kernel<VT, LPG, LPA, FUSED><<<grid, kTileThreads, smem, st>>>(a);
+    }
+    return check_launch();
+}
+
+template <typename VT, bool FUSED, bool BWD>
+int launch_tile_lanes(const TileArgs &a, const TilePlan &p, int grid, cudaStream_t st)
+{
+#define MSDA_TILE_CASE(LPG_)                                                                                  \
+    case LPG_:                                                                                                \
+        return p.lpa == 16 ? launch_tile_inst<VT, LPG_, 16, FUSED, BWD>(a, grid, p.smem, st)                  \
+                           : launch_tile_inst<VT, LPG_, 32, FUSED, BWD>(a, grid, p.smem, st);
+    switch (p.lpg) {
+        MSDA_TILE_CASE(4)
+        MSDA_TILE_CASE(8)
+        MSDA_TILE_CASE(16)
+        default: MSDA_TILE_CASE(32)
+    }
+#undef MSDA_TILE_CASE
+}
+
+template <bool FUSED, bool BWD> int launch_tile(const TileArgs &a, const TilePlan &p, int dtype, cudaStream_t st)
+{
+    const int grid = a.N * a.M * a.chunks;
+    return dtype == MSDA_F32 ? launch_tile_lanes<float, FUSED, BWD>(a, p, grid, st)
+                             : launch_tile_lanes<__nv_bfloat16, FUSED, BWD>(a, p, grid, st);
 }
 
 int generic_grid(long long total)
@@ -180,6 +313,17 @@ int msda_ms_deform_attn_forward(const void *value, const int64_t *spatial_shapes
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const bool one_d = (flags & MSDA_FLAG_ASSUME_1D) != 0;
     const int lpg = (flags & MSDA_FLAG_FORCE_GENERIC) ? 0 : fast_lpg(D, dtype);
+    if (one_d && !(flags & MSDA_FLAG_FORCE_GENERIC)) {
+        const TilePlan tp = tile_plan(d, dtype, false);
+        if (tp.ok) {
+            TileArgs a{};
+            a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
+            a.loc = static_cast<const float *>(sampling_loc); a.attn = static_cast<const float *>(attn_weight);
+            a.out = output;
+            fill_tile_args(a, d, tp, pad_mode);
+            return launch_tile<false, false>(a, tp, dtype, st);
+        }
+    }
     if (one_d && lpg) {
         FastArgs a{};
         a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
@@ -189,6 +333,7 @@ int msda_ms_deform_attn_forward(const void *value, const int64_t *spatial_shapes
         a.total_units = N * Lq * M;
         int grid;
         fast_grid(a.total_units, lpg, grid, a.units_per_cta);
+        a.head_major = head_major_env();
         return dtype == MSDA_F32 ? launch_fast_fwd<float, false>(a, lpg, grid, st)
                                  : launch_fast_fwd<__nv_bfloat16, false>(a, lpg, grid, st);
     }
@@ -227,7 +372,16 @@ int msda_ms_deform_attn_backward(const void *value, const int64_t *spatial_shape
     const bool one_d = (flags & MSDA_FLAG_ASSUME_1D) != 0;
     const int lpg = (flags & MSDA_FLAG_FORCE_GENERIC) ? 0 : fast_lpg(D, dtype);
     int rc;
-    if (one_d && lpg) {
+    const TilePlan tp = (one_d && !(flags & MSDA_FLAG_FORCE_GENERIC)) ? tile_plan(d, dtype, true) : TilePlan{};
+    if (tp.ok) {
+        TileArgs a{};
+        a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
+        a.loc = static_cast<const float *>(sampling_loc); a.attn = static_cast<const float *>(attn_weight);
+        a.grad_out = grad_output; a.gv_acc = static_cast<float *>(acc);
+        a.grad_loc = static_cast<float *>(grad_sampling_loc); a.grad_attn = static_cast<float *>(grad_attn_weight);
+        fill_tile_args(a, d, tp, pad_mode);
+        rc = launch_tile<false, true>(a, tp, dtype, st);
+    } else if (one_d && lpg) {
         FastArgs a{};
         a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
         a.loc = static_cast<const float *>(sampling_loc); a.attn = static_cast<const float *>(attn_weight);
@@ -237,6 +391,7 @@ int msda_ms_deform_attn_backward(const void *value, const int64_t *spatial_shape
         a.total_units = N * Lq * M;
         int grid;
         fast_grid(a.total_units, lpg, grid, a.units_per_cta);
+        a.head_major = head_major_env();
         rc = dtype == MSDA_F32 ? launch_fast_bwd<float, false>(a, lpg, grid, st)
                                : launch_fast_bwd<__nv_bfloat16, false>(a, lpg, grid, st);
     } else {
@@ -272,6 +427,17 @@ int msda_fused_forward(const void *value, const int64_t *temporal_shapes, const 
     const int lpg = fast_lpg(D, dtype);
     if (!lpg) return MSDA_ERR_UNSUPPORTED;   // callers fall back to the unfused entry points (still CUDA)
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    {
+        const TilePlan tp = tile_plan(d, dtype, false);
+        if (tp.ok) {
+            TileArgs t{};
+            t.value = value; t.shapes = temporal_shapes; t.lsi = level_start_index; t.shapes_stride = 1;
+            t.ref = reference_points; t.offs = sampling_offsets; t.logits = attn_logits; t.R = R;
+            t.out = output;
+            fill_tile_args(t, d, tp, pad_mode);
+            return launch_tile<true, false>(t, tp, dtype, st);
+        }
+    }
     FastArgs a{};
     a.value = value; a.shapes = temporal_shapes; a.lsi = level_start_index; a.shapes_stride = 1;
     a.ref = reference_points; a.offs = sampling_offsets; a.logits = attn_logits; a.R = R;
@@ -280,6 +446,7 @@ int msda_fused_forward(const void *value, const int64_t *temporal_shapes, const 
     a.total_units = N * Lq * M;
     int grid;
     fast_grid(a.total_units, lpg, grid, a.units_per_cta);
+    a.head_major = head_major_env();
     return dtype == MSDA_F32 ? launch_fast_fwd<float, true>(a, lpg, grid, st)
                              : launch_fast_fwd<__nv_bfloat16, true>(a, lpg, grid, st);
 }
@@ -310,6 +477,21 @@ int msda_fused_backward(const void *value, const int64_t *temporal_shapes, const
     if (int e = memset_async(acc, (size_t)nv * 4, st)) return e;
     if (grad_reference_points)
         if (int e = memset_async(grad_reference_points, (size_t)N * Lq * L * R * 4, st)) return e;
+    {
+        const TilePlan tp = tile_plan(d, dtype, true);
+        if (tp.ok) {
+            TileArgs t{};
+            t.value = value; t.shapes = temporal_shapes; t.lsi = level_start_index; t.shapes_stride = 1;
+            t.ref = reference_points; t.offs = sampling_offsets; t.logits = attn_logits; t.R = R;
+            t.grad_out = grad_output; t.gv_acc = static_cast<float *>(acc);
+            t.grad_ref = grad_reference_points; t.grad_offs = grad_sampling_offsets; t.grad_logits = grad_attn_logits;
+            fill_tile_args(t, d, tp, pad_mode);
+            const int trc = launch_tile<true, true>(t, tp, dtype, st);
+            if (trc) return trc;
+            if (dtype == MSDA_BF16) return finish_bf16(static_cast<const float *>(acc), grad_value, nv, st);
+            return MSDA_OK;
+        }
+    }
     FastArgs a{};
     a.value = value; a.shapes = temporal_shapes; a.lsi = level_start_index; a.shapes_stride = 1;
     a.ref = reference_points; a.offs = sampling_offsets; a.logits = attn_logits; a.R = R;
@@ -319,6 +501,7 @@ int msda_fused_backward(const void *value, const int64_t *temporal_shapes, const
     a.total_units = N * Lq * M;
     int grid;
     fast_grid(a.total_units, lpg, grid, a.units_per_cta);
+    a.head_major = head_major_env();
     const int rc = dtype == MSDA_F32 ? launch_fast_bwd<float, true>(a, lpg, grid, st)
                                      : launch_fast_bwd<__nv_bfloat16, true>(a, lpg, grid, st);
     if (rc) return rc;

@@ -53,6 +53,7 @@ struct FastArgs {
     int pad_mode;
     int total_units;     // N*Lq*M (< 2^31, checked by the launcher)
     int units_per_cta;
+    int head_major;      // iterate units as (n, m, q) instead of storage order (n, q, m)
 };
 
 constexpr int kFastThreads = 128;
@@ -191,10 +192,21 @@ __global__ void __launch_bounds__(kFastThreads) msda_fwd_fast_kernel(const FastA
     const int d_step = LPG * CH;
 
     for (int ubase = cta_begin + warp * G; ubase < cta_end; ubase += kFastWarps * G) {
-        const int u = ubase + g;
-        const bool active = u < cta_end;
-        const int nq = active ? u / a.M : 0;
-        const int m = active ? u - nq * a.M : 0;
+        const int wi = ubase + g;
+        const bool active = wi < cta_end;
+        int u, nq, m;
+        if (a.head_major) {   // work order (n, m, q): neighbouring queries of ONE head share value rows
+            const int nm = active ? wi / a.Lq : 0;
+            const int q = active ? wi - nm * a.Lq : 0;
+            const int nn = nm / a.M;
+            m = nm - nn * a.M;
+            nq = nn * a.Lq + q;
+            u = nq * a.M + m;
+        } else {
+            u = wi;
+            nq = active ? u / a.M : 0;
+            m = active ? u - nq * a.M : 0;
+        }
         const long long n = nq / a.Lq;
         float sm_max = 0.f, sm_inv = 0.f;
         if (FUSED) softmax_stats<LPG>(a.logits + (long long)u * LP, active, j, LP, sm_max, sm_inv);
@@ -266,10 +278,21 @@ __global__ void __launch_bounds__(kFastThreads) msda_bwd_fast_kernel(const FastA
     const bool p_pow2 = (a.P & (a.P - 1)) == 0 && a.P <= LPG;
 
     for (int ubase = cta_begin + warp * G; ubase < cta_end; ubase += kFastWarps * G) {
-        const int u = ubase + g;
-        const bool active = u < cta_end;
-        const int nq = active ? u / a.M : 0;
-        const int m = active ? u - nq * a.M : 0;
+        const int wi = ubase + g;
+        const bool active = wi < cta_end;
+        int u, nq, m;
+        if (a.head_major) {   // work order (n, m, q): neighbouring queries of ONE head share value rows
+            const int nm = active ? wi / a.Lq : 0;
+            const int q = active ? wi - nm * a.Lq : 0;
+            const int nn = nm / a.M;
+            m = nm - nn * a.M;
+            nq = nn * a.Lq + q;
+            u = nq * a.M + m;
+        } else {
+            u = wi;
+            nq = active ? u / a.M : 0;
+            m = active ? u - nq * a.M : 0;
+        }
         const long long n = nq / a.Lq;
         float sm_max = 0.f, sm_inv = 0.f;
         if (FUSED) softmax_stats<LPG>(a.logits + (long long)u * LP, active, j, LP, sm_max, sm_inv);
