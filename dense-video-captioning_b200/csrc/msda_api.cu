@@ -11,6 +11,7 @@
 #include "msda_fast.cuh"
 #include "msda_generic.cuh"
 #include "msda_tile.cuh"
+#include "msda_lean.cuh"
 
 using namespace msda;
 
@@ -227,6 +228,100 @@ template <bool FUSED, bool BWD> int launch_tile(const TileArgs &a, const TilePla
                              : launch_tile_lanes<__nv_bfloat16, FUSED, BWD>(a, p, grid, st);
 }
 
+// ---- lean kernels (L*P <= 32): planning and launch ---------------------------------------------------
+
+struct LeanPlan {
+    bool ok;
+    int lpg, nch, lpa, Q, chunks, win_rows;
+    size_t smem;
+};
+
+LeanPlan lean_plan(const Dims &d, int dtype, bool backward)
+{
+    static const int use_lean = env_int("MSDA_LEAN", 1);
+    static const int win_kb = env_int("MSDA_WIN_KB", 64);
+    static const int passes_env = env_int("MSDA_PASSES", 0);
+    LeanPlan p{};
+    if (!use_lean || dtype == MSDA_F64) return p;
+    const int LP = d.L * d.P;
+    const int rb = d.D * (dtype == MSDA_BF16 ? 2 : 4);
+    if (LP > 32 || rb % 16 != 0) return p;
+    const int chunks16 = rb / 16;
+    if (chunks16 == 4) { p.lpg = 4; p.nch = 1; }
+    else if (chunks16 == 8 || chunks16 == 16 || chunks16 == 32) { p.lpg = 8; p.nch = chunks16 / 8; }
+    else return p;
+    if (d.N > 65535 || d.M > 65535 || d.S >= (1 << 26)) return p;
+    if ((long long)d.N * d.Lq * d.M * LP >= (1ll << 30)) return p;   // 32-bit sample indices
+    p.lpa = LP <= 16 ? 16 : 32;
+    const int upp = kLeanWarps * (32 / p.lpa);
+    int passes = kLeanPasses;
+    // small problems: fewer queries per CTA so that every SM gets work
+    while (passes > 1 && (long long)d.N * d.M * ((d.Lq + upp * passes - 1) / (upp * passes)) < 2 * kNumSMs) passes >>= 1;
+    if (passes_env > 0 && passes_env <= kLeanPasses) passes = passes_env;
+    p.Q = upp * passes;
+    p.chunks = (d.Lq + p.Q - 1) / p.Q;
+    if (backward) {
+        p.smem = bwd_lean_smem_bytes(p.Q, p.lpa, d.S, rb);
+        if (p.smem > kMaxDynSmem) return p;
+    } else {
+        const size_t recs = (size_t)p.Q * p.lpa * sizeof(int4);
+        const size_t win = (size_t)win_kb * 1024;
+        p.win_rows = (int)(win / rb);
+        if (p.win_rows > d.S) p.win_rows = d.S;   // the whole head slice fits
+        p.smem = recs + (size_t)p.win_rows * rb;
+        if (p.smem > kMaxDynSmem) return p;
+    }
+    p.ok = true;
+    return p;
+}
+
+void fill_lean_args(TileArgs &a, const Dims &d, const LeanPlan &p, int pad_mode)
+{
+    a.N = d.N; a.S = d.S; a.M = d.M; a.D = d.D; a.L = d.L; a.Lq = d.Lq; a.P = d.P;
+    a.pad_mode = pad_mode;
+    a.LP = d.L * d.P;
+    a.LPpad = p.lpa;
+    a.invP = 1.f / (float)d.P;
+    a.Q = p.Q;
+    a.chunks = p.chunks;
+    a.win_rows = p.win_rows;
+}
+
+template <typename VT, int LPG, int NCH, int LPA, bool FUSED, bool BWD>
+int launch_lean_inst(const TileArgs &a, const LeanPlan &p, cudaStream_t st)
+{
+    static unsigned long long done = 0;
+    const dim3 grid(p.chunks, a.M, a.N);
+    if (BWD) {
+        if (int e = allow_big_smem(msda_bwd_lean_kernel<VT, LPG, NCH, LPA, FUSED>, done)) return e;
+        msda_bwd_lean_kernel<VT, LPG, NCH, LPA, FUSED><<<grid, kLeanThreads, p.smem, st>>>(a);
+    } else {
+        if (int e = allow_big_smem(msda_fwd_lean_kernel<VT, LPG, NCH, LPA, FUSED>, done)) return e;
+        msda_fwd_lean_kernel<VT, LPG, NCH, LPA, FUSED><<<grid, kLeanThreads, p.smem, st>>>(a);
+    }
+    return check_launch();
+}
+
+template <typename VT, bool FUSED, bool BWD> int launch_lean_shape(const TileArgs &a, const LeanPlan &p, cudaStream_t st)
+{
+#define MSDA_LEAN_CASE(LPG_, NCH_)                                                                       \
+    if (p.lpg == LPG_ && p.nch == NCH_)                                                                  \
+        return p.lpa == 16 ? launch_lean_inst<VT, LPG_, NCH_, 16, FUSED, BWD>(a, p, st)                  \
+                           : launch_lean_inst<VT, LPG_, NCH_, 32, FUSED, BWD>(a, p, st);
+    MSDA_LEAN_CASE(4, 1)
+    MSDA_LEAN_CASE(8, 1)
+    MSDA_LEAN_CASE(8, 2)
+    MSDA_LEAN_CASE(8, 4)
+#undef MSDA_LEAN_CASE
+    return MSDA_ERR_UNSUPPORTED;
+}
+
+template <bool FUSED, bool BWD> int launch_lean(const TileArgs &a, const LeanPlan &p, int dtype, cudaStream_t st)
+{
+    return dtype == MSDA_F32 ? launch_lean_shape<float, FUSED, BWD>(a, p, st)
+                             : launch_lean_shape<__nv_bfloat16, FUSED, BWD>(a, p, st);
+}
+
 int generic_grid(long long total)
 {
     long long blocks = (total + 255) / 256;
@@ -314,12 +409,17 @@ int msda_ms_deform_attn_forward(const void *value, const int64_t *spatial_shapes
     const bool one_d = (flags & MSDA_FLAG_ASSUME_1D) != 0;
     const int lpg = (flags & MSDA_FLAG_FORCE_GENERIC) ? 0 : fast_lpg(D, dtype);
     if (one_d && !(flags & MSDA_FLAG_FORCE_GENERIC)) {
-        const TilePlan tp = tile_plan(d, dtype, false);
-        if (tp.ok) {
+        const LeanPlan lp = lean_plan(d, dtype, false);
+        const TilePlan tp = lp.ok ? TilePlan{} : tile_plan(d, dtype, false);
+        if (lp.ok || tp.ok) {
             TileArgs a{};
             a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
             a.loc = static_cast<const float *>(sampling_loc); a.attn = static_cast<const float *>(attn_weight);
             a.out = output;
+            if (lp.ok) {
+                fill_lean_args(a, d, lp, pad_mode);
+                return launch_lean<false, false>(a, lp, dtype, st);
+            }
             fill_tile_args(a, d, tp, pad_mode);
             return launch_tile<false, false>(a, tp, dtype, st);
         }
@@ -372,15 +472,22 @@ int msda_ms_deform_attn_backward(const void *value, const int64_t *spatial_shape
     const bool one_d = (flags & MSDA_FLAG_ASSUME_1D) != 0;
     const int lpg = (flags & MSDA_FLAG_FORCE_GENERIC) ? 0 : fast_lpg(D, dtype);
     int rc;
-    const TilePlan tp = (one_d && !(flags & MSDA_FLAG_FORCE_GENERIC)) ? tile_plan(d, dtype, true) : TilePlan{};
-    if (tp.ok) {
+    const bool try_chunked = one_d && !(flags & MSDA_FLAG_FORCE_GENERIC);
+    const LeanPlan lp = try_chunked ? lean_plan(d, dtype, true) : LeanPlan{};
+    const TilePlan tp = (try_chunked && !lp.ok) ? tile_plan(d, dtype, true) : TilePlan{};
+    if (lp.ok || tp.ok) {
         TileArgs a{};
         a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
         a.loc = static_cast<const float *>(sampling_loc); a.attn = static_cast<const float *>(attn_weight);
         a.grad_out = grad_output; a.gv_acc = static_cast<float *>(acc);
         a.grad_loc = static_cast<float *>(grad_sampling_loc); a.grad_attn = static_cast<float *>(grad_attn_weight);
-        fill_tile_args(a, d, tp, pad_mode);
-        rc = launch_tile<false, true>(a, tp, dtype, st);
+        if (lp.ok) {
+            fill_lean_args(a, d, lp, pad_mode);
+            rc = launch_lean<false, true>(a, lp, dtype, st);
+        } else {
+            fill_tile_args(a, d, tp, pad_mode);
+            rc = launch_tile<false, true>(a, tp, dtype, st);
+        }
     } else if (one_d && lpg) {
         FastArgs a{};
         a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
@@ -428,12 +535,17 @@ int msda_fused_forward(const void *value, const int64_t *temporal_shapes, const 
     if (!lpg) return MSDA_ERR_UNSUPPORTED;   // callers fall back to the unfused entry points (still CUDA)
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     {
-        const TilePlan tp = tile_plan(d, dtype, false);
-        if (tp.ok) {
+        const LeanPlan lp = lean_plan(d, dtype, false);
+        const TilePlan tp = lp.ok ? TilePlan{} : tile_plan(d, dtype, false);
+        if (lp.ok || tp.ok) {
             TileArgs t{};
             t.value = value; t.shapes = temporal_shapes; t.lsi = level_start_index; t.shapes_stride = 1;
             t.ref = reference_points; t.offs = sampling_offsets; t.logits = attn_logits; t.R = R;
             t.out = output;
+            if (lp.ok) {
+                fill_lean_args(t, d, lp, pad_mode);
+                return launch_lean<true, false>(t, lp, dtype, st);
+            }
             fill_tile_args(t, d, tp, pad_mode);
             return launch_tile<true, false>(t, tp, dtype, st);
         }
@@ -478,15 +590,22 @@ int msda_fused_backward(const void *value, const int64_t *temporal_shapes, const
     if (grad_reference_points)
         if (int e = memset_async(grad_reference_points, (size_t)N * Lq * L * R * 4, st)) return e;
     {
-        const TilePlan tp = tile_plan(d, dtype, true);
-        if (tp.ok) {
+        const LeanPlan lp = lean_plan(d, dtype, true);
+        const TilePlan tp = lp.ok ? TilePlan{} : tile_plan(d, dtype, true);
+        if (lp.ok || tp.ok) {
             TileArgs t{};
             t.value = value; t.shapes = temporal_shapes; t.lsi = level_start_index; t.shapes_stride = 1;
             t.ref = reference_points; t.offs = sampling_offsets; t.logits = attn_logits; t.R = R;
             t.grad_out = grad_output; t.gv_acc = static_cast<float *>(acc);
             t.grad_ref = grad_reference_points; t.grad_offs = grad_sampling_offsets; t.grad_logits = grad_attn_logits;
-            fill_tile_args(t, d, tp, pad_mode);
-            const int trc = launch_tile<true, true>(t, tp, dtype, st);
+            int trc;
+            if (lp.ok) {
+                fill_lean_args(t, d, lp, pad_mode);
+                trc = launch_lean<true, true>(t, lp, dtype, st);
+            } else {
+                fill_tile_args(t, d, tp, pad_mode);
+                trc = launch_tile<true, true>(t, tp, dtype, st);
+            }
             if (trc) return trc;
             if (dtype == MSDA_BF16) return finish_bf16(static_cast<const float *>(acc), grad_value, nv, st);
             return MSDA_OK;

@@ -1,0 +1,553 @@
+// msda_lean.cuh -- the production kernels of the 1-D temporal MSDeformAttn hot path for sm_100a.
+//
+// Same algorithm as msda_tile.cuh (chunk of Q queries of one head per CTA; forward = value window staged
+// in shared memory by cp.async.bulk + LDS.128 gather; backward = samples counting-sorted by value row, one
+// lane group per row), re-written for instruction economy after ncu showed both tile kernels issue-bound
+// (profiles/r1_notes.md): every lane decodes at most ONE sample per query (L*P <= 32), so level, T_l,
+// level start are per-lane constants, all indices are 32-bit, decoded samples stay in registers between
+// phases, each lane owns NCH 16-byte chunks of a value row (fewer shuffle steps per dot product and
+// fewer address computations per FFMA2).
+//
+// Replaces, for H_l == 1: ms_deformable_im2col_gpu_kernel (ms_deform_im2col_cuda.cuh:238-300), the
+// col2im kernels (cuh:302-921) and, FUSED, pdvc/ops/modules/ms_deform_attn.py:100-116.
+#pragma once
+#include "msda_tile.cuh"
+
+namespace msda {
+
+constexpr int kLeanThreads = 256;
+constexpr int kLeanWarps = kLeanThreads / 32;
+constexpr int kLeanPasses = 4;   // units decoded per lane group and CTA (Q = kLeanPasses * units per pass)
+
+// per-lane constants of the decode phase: lane j of a unit's group always decodes sample j = (l, p)
+struct LaneLevel {
+    int l, T, start;
+    float tf;
+    bool live;   // j < L*P
+};
+
+__device__ __forceinline__ LaneLevel lane_level(const TileArgs &a, int j)
+{
+    LaneLevel c;
+    c.live = j < a.LP;
+    c.l = c.live ? j / a.P : 0;
+    c.T = (int)__ldg(a.shapes + (a.shapes_stride == 2 ? 2 * c.l + 1 : c.l));
+    c.start = (int)__ldg(a.lsi + c.l);
+    c.tf = (float)c.T;
+    return c;
+}
+
+// raw per-sample inputs (issued for all passes before anything is consumed)
+struct RawSample {
+    float x;   // fused: offset            unfused: location
+    float y;   // fused: attention logit   unfused: attention weight
+    float r0;  // fused: reference point
+    float r1;  // fused, R == 2: reference length
+};
+
+template <bool FUSED>
+__device__ __forceinline__ RawSample load_raw(const TileArgs &a, const LaneLevel &c, int nq, int sidx, bool on)
+{
+    RawSample r;
+    r.x = r.y = r.r0 = r.r1 = 0.f;
+    if (on) {
+        if (FUSED) {
+            r.x = __ldg(a.offs + sidx);
+            r.y = __ldg(a.logits + sidx);
+            const float *rp = a.ref + (nq * a.L + c.l) * a.R;
+            r.r0 = __ldg(rp);
+            if (a.R == 2) r.r1 = __ldg(rp + 1);
+        } else {
+            r.x = __ldg(a.loc + 2 * sidx);
+            r.y = __ldg(a.attn + sidx);
+        }
+    }
+    return r;
+}
+
+struct Decoded {
+    int r0, r1;      // slice rows
+    float w0, w1;    // interpolation weights (0 for a missing tap)
+    float s0, s1;    // -gate / +gate
+    float A;         // attention weight
+    float dxdoff;    // fused: d(loc)/d(offset)
+};
+
+// softmax over the LPA lanes of a unit's group (FUSED) + sampling geometry; all lanes of the warp call it
+template <bool FUSED, int LPA>
+__device__ __forceinline__ Decoded decode(const TileArgs &a, const LaneLevel &c, const RawSample &raw, bool on)
+{
+    Decoded d;
+    float hi, lo;
+    if (FUSED) {
+        const float mx = group_max<LPA>(on ? raw.y : -INFINITY);
+        const float e = on ? __expf(raw.y - mx) : 0.f;
+        const float sum = group_sum<LPA>(e);
+        d.A = sum > 0.f ? __fdividef(e, sum) : 0.f;
+        const float p = raw.r0 * c.tf;
+        const float plo = fmaf(raw.r0, c.tf, -p);
+        float add;
+        if (a.R == 1) {   // x = ref0 + off / T_l          (ms_deform_attn.py:103-106)
+            add = raw.x - 0.5f;
+            d.dxdoff = __fdividef(1.f, c.tf);
+        } else {          // x = ref0 + off / P * ref1 * 0.5 (ms_deform_attn.py:107-109)
+            d.dxdoff = raw.r1 * (0.5f * a.invP);
+            add = fmaf(raw.x * d.dxdoff, c.tf, -0.5f);
+        }
+        float err;
+        two_sum(p, add, hi, err);
+        lo = plo + err;
+    } else {
+        d.A = raw.y;
+        d.dxdoff = 0.f;
+        pix_from_loc(raw.x, c.T, hi, lo);
+    }
+    const Tap1D t = locate_1d(hi, lo, c.T, a.pad_mode);
+    d.r0 = c.start + t.i0;
+    d.r1 = c.start + t.i1;
+    d.w0 = t.w0; d.w1 = t.w1; d.s0 = t.s0; d.s1 = t.s1;
+    return d;
+}
+
+// value / grad rows: lane j of a row group owns the 16-byte chunks c*LPG + j, c < NCH
+template <typename VT, int LPG, int NCH> struct RowIO {
+    static constexpr int CH = Vec16<VT>::CH;
+    static constexpr int NF = NCH * CH;   // floats per lane
+    __device__ __forceinline__ static void load_smem(const unsigned char *p, float (&v)[NF])
+    {
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            float t[CH];
+            VecPlain<VT>::load(p + c * LPG * 16, t);
+#pragma unroll
+            for (int k = 0; k < CH; ++k) v[c * CH + k] = t[k];
+        }
+    }
+    __device__ __forceinline__ static void load_gmem(const VT *p, float (&v)[NF])
+    {
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            float t[CH];
+            Vec16<VT>::load(p + c * LPG * CH, t);
+#pragma unroll
+            for (int k = 0; k < CH; ++k) v[c * CH + k] = t[k];
+        }
+    }
+    __device__ __forceinline__ static void store_gmem(VT *p, const float (&v)[NF])
+    {
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            float t[CH];
+#pragma unroll
+            for (int k = 0; k < CH; ++k) t[k] = v[c * CH + k];
+            Vec16<VT>::store(p + c * LPG * CH, t);
+        }
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// forward.  grid = (chunks, M, N); dynamic shared memory = [ records int4 x Q*LPA | value window ]
+// ---------------------------------------------------------------------------------------------
+template <typename VT, int LPG, int NCH, int LPA, bool FUSED>
+__global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileArgs a)
+{
+    using IO = RowIO<VT, LPG, NCH>;
+    constexpr int CH = Vec16<VT>::CH;
+    constexpr int NF = IO::NF;
+    constexpr int G = 32 / LPG;     // units per warp in the gather phase
+    constexpr int UPW = 32 / LPA;   // units per warp in the decode phase
+    constexpr int UPP = kLeanWarps * UPW;
+    extern __shared__ __align__(128) unsigned char dsm[];
+    __shared__ int win_lo[kMaxLevels], win_hi[kMaxLevels], win_base[kMaxLevels];
+    __shared__ unsigned long long mbar;
+    __shared__ int win_ok;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int n = blockIdx.z, m = blockIdx.y;
+    const int q0 = blockIdx.x * a.Q;
+    const int Qc = min(a.Q, a.Lq - q0);
+    const int MD = a.M * a.D;
+    constexpr int rb = LPG * NCH * 16;   // bytes per row of one head (= D * sizeof(VT))
+    int4 *recs = reinterpret_cast<int4 *>(dsm);
+    unsigned char *win = dsm + (size_t)a.Q * LPA * sizeof(int4);
+
+    if (tid < a.L) { win_lo[tid] = INT_MAX; win_hi[tid] = -1; }
+    if (tid == 0) mbar_init(&mbar, 1);
+
+    // ---- decode: lane (g, j) handles sample j of units warp*UPW + g + t*UPP, t < passes ----
+    const int g1 = lane / LPA, j1 = lane % LPA;
+    const LaneLevel lc = lane_level(a, j1);
+    const int passes = (Qc + UPP - 1) / UPP;
+    RawSample raw[kLeanPasses];
+#pragma unroll
+    for (int t = 0; t < kLeanPasses; ++t) {
+        const int ul = t * UPP + warp * UPW + g1;
+        const bool on = lc.live && ul < Qc;
+        const int nq = n * a.Lq + q0 + ul;
+        raw[t] = load_raw<FUSED>(a, lc, nq, (nq * a.M + m) * a.LP + j1, on);
+    }
+    __syncthreads();   // win_lo / win_hi / mbar initialised
+    int r0[kLeanPasses], r1[kLeanPasses];
+    float c0[kLeanPasses], c1[kLeanPasses];
+    int lo = INT_MAX, hi = -1;
+#pragma unroll
+    for (int t = 0; t < kLeanPasses; ++t) {
+        r0[t] = r1[t] = -1;
+        c0[t] = c1[t] = 0.f;
+        if (t < passes) {   // block-uniform
+            const int ul = t * UPP + warp * UPW + g1;
+            const bool on = lc.live && ul < Qc;
+            const Decoded d = decode<FUSED, LPA>(a, lc, raw[t], on);
+            const float k0 = d.A * d.w0, k1 = d.A * d.w1;
+            if (on && (k0 != 0.f || k1 != 0.f)) {
+                r0[t] = d.r0; r1[t] = d.r1; c0[t] = k0; c1[t] = k1;
+                lo = min(lo, d.r0);
+                hi = max(hi, d.r1);
+            }
+        }
+    }
+    if (hi >= 0) { atomicMin(&win_lo[lc.l], lo); atomicMax(&win_hi[lc.l], hi); }
+    __syncthreads();
+    if (tid == 0) {
+        int tot = 0;
+        for (int l = 0; l < a.L; ++l) {
+            win_base[l] = tot - win_lo[l];   // window row of slice row r at level l: win_base[l] + r
+            if (win_hi[l] >= win_lo[l]) tot += win_hi[l] - win_lo[l] + 1;
+        }
+        const int ok = (tot > 0 && tot <= a.win_rows) ? 1 : 0;
+        win_ok = ok;
+        if (ok) mbar_expect_tx(&mbar, (unsigned)tot * (unsigned)rb);
+    }
+    __syncthreads();
+    const bool staged = win_ok != 0;
+    const VT *vslice = static_cast<const VT *>(a.value) + (size_t)n * a.S * MD + m * a.D;
+    if (staged) {
+        for (int l = 0; l < a.L; ++l)
+            for (int r = win_lo[l] + tid; r <= win_hi[l]; r += kLeanThreads)
+                bulk_g2s(win + (win_base[l] + r) * rb, vslice + (size_t)r * MD, (unsigned)rb, &mbar);
+    }
+    {   // final records: byte offsets into the window (staged) or element offsets into the slice
+        const int base = staged ? win_base[lc.l] : 0;
+        const int scale = staged ? rb : MD;
+#pragma unroll
+        for (int t = 0; t < kLeanPasses; ++t) {
+            const int ul = t * UPP + warp * UPW + g1;
+            if (t < passes && ul < Qc) {
+                const bool livet = r0[t] >= 0;
+                recs[ul * LPA + j1] = make_int4(livet ? (base + r0[t]) * scale : 0, livet ? (base + r1[t]) * scale : 0,
+                                                __float_as_int(c0[t]), __float_as_int(c1[t]));
+            }
+        }
+    }
+    __syncthreads();
+    if (staged) mbar_wait(&mbar, 0);
+
+    // ---- gather ----
+    {
+        const int g = lane / LPG, j = lane % LPG;
+        VT *out = static_cast<VT *>(a.out);
+        const unsigned char *wlane = win + j * 16;
+        const VT *vlane = vslice + j * CH;
+        const int LP4 = (a.LP + 3) & ~3;
+        for (int ul0 = warp * G; ul0 < Qc; ul0 += kLeanWarps * G) {
+            const int ul = ul0 + g;
+            const bool active = ul < Qc;
+            const int4 *rp = recs + (active ? ul : 0) * LPA;
+            float acc[NF];
+#pragma unroll
+            for (int k = 0; k < NF; ++k) acc[k] = 0.f;
+            for (int s = 0; s < LP4; s += 4) {
+                int4 r[4];
+#pragma unroll
+                for (int b = 0; b < 4; ++b) r[b] = rp[s + b];
+                if (staged) {
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) {
+                        float v0[NF], v1[NF];
+                        IO::load_smem(wlane + r[b].x, v0);
+                        IO::load_smem(wlane + r[b].y, v1);
+                        axpy<NF>(acc, __int_as_float(r[b].z), v0);
+                        axpy<NF>(acc, __int_as_float(r[b].w), v1);
+                    }
+                } else {
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) {
+                        float v0[NF], v1[NF];
+                        IO::load_gmem(vlane + r[b].x, v0);
+                        IO::load_gmem(vlane + r[b].y, v1);
+                        axpy<NF>(acc, __int_as_float(r[b].z), v0);
+                        axpy<NF>(acc, __int_as_float(r[b].w), v1);
+                    }
+                }
+            }
+            if (active) IO::store_gmem(out + (size_t)((n * a.Lq + q0 + ul) * a.M + m) * a.D + j * CH, acc);
+        }
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// backward.  grid = (chunks, M, N).  Dynamic shared memory (QS = Q * LPA sample slots):
+//   Gs    Q x D VT          grad_out rows of the chunk (this head)
+//   ent   (2*QS + 2) int4   samples in value-row order, every row's run padded to an even length:
+//                           {slot | unit << 16, A*wa, A*wb, -};  ent[2*QS] is a permanent no-op entry
+//   dots  (QS + 1) float2   {G.V[r], G.V[r+1]} per sample slot (+1 sink for the no-op entries)
+//   rows  QS int            occupied rows: r | needs_row_r+1 << 30
+//   start (S + 1) int       histogram of first rows -> start of each row's run in ent
+// ---------------------------------------------------------------------------------------------
+constexpr int kRowFlagShift = 30;
+
+__host__ __device__ inline size_t bwd_lean_smem_bytes(int Q, int LPA, int S, int rb)
+{
+    const size_t QS = (size_t)Q * LPA;
+    return (size_t)Q * rb + (2 * QS + 2) * 16 + (QS + 1 + 1) * 8 + QS * 4 + ((size_t)S + 1 + 3) / 4 * 16;
+}
+
+template <typename VT, int LPG, int NCH, int LPA, bool FUSED>
+__global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const TileArgs a)
+{
+    using IO = RowIO<VT, LPG, NCH>;
+    constexpr int CH = Vec16<VT>::CH;
+    constexpr int NF = IO::NF;
+    constexpr int NG = kLeanThreads / LPG;   // row groups per CTA
+    constexpr int UPW = 32 / LPA;
+    constexpr int UPP = kLeanWarps * UPW;
+    constexpr int rb = LPG * NCH * 16;
+    extern __shared__ __align__(128) unsigned char dsm[];
+    __shared__ int wsum[kLeanWarps];
+    __shared__ int n_active_s;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int n = blockIdx.z, m = blockIdx.y;
+    const int q0 = blockIdx.x * a.Q;
+    const int Qc = min(a.Q, a.Lq - q0);
+    const int MD = a.M * a.D;
+    const int QS = a.Q * LPA;
+    unsigned char *Gs = dsm;
+    int4 *ent = reinterpret_cast<int4 *>(Gs + (size_t)a.Q * rb);
+    float2 *dots = reinterpret_cast<float2 *>(ent + 2 * QS + 2);
+    int *rows = reinterpret_cast<int *>(dots + QS + 2);
+    int *start = rows + QS;
+
+    // ---- raw inputs of this lane's samples, grad_out rows (async), histogram reset ----
+    const int g1 = lane / LPA, j1 = lane % LPA;
+    const LaneLevel lc = lane_level(a, j1);
+    const int passes = (Qc + UPP - 1) / UPP;
+    RawSample raw[kLeanPasses];
+#pragma unroll
+    for (int t = 0; t < kLeanPasses; ++t) {
+        const int ul = t * UPP + warp * UPW + g1;
+        const bool on = lc.live && ul < Qc;
+        const int nq = n * a.Lq + q0 + ul;
+        raw[t] = load_raw<FUSED>(a, lc, nq, (nq * a.M + m) * a.LP + j1, on);
+    }
+    {
+        const unsigned char *gsrc =
+            static_cast<const unsigned char *>(a.grad_out) + ((size_t)(n * a.Lq + q0) * a.M + m) * rb;
+        constexpr int VPR = rb / 16;   // 16-byte vectors per row
+        for (int v = tid; v < Qc * VPR; v += kLeanThreads) {
+            const int ul = v / VPR, jj = v % VPR;
+            cp_async16(Gs + ul * rb + jj * 16, gsrc + (size_t)ul * a.M * rb + jj * 16);
+        }
+    }
+    for (int i = tid; i <= a.S; i += kLeanThreads) start[i] = 0;
+    if (tid == 0) ent[2 * QS] = make_int4(QS, 0, 0, 0);   // no-op entry: unit 0, zero weights, sink slot
+    __syncthreads();
+
+    // ---- decode + histogram of first rows ----
+    int key[kLeanPasses], rank[kLeanPasses];
+    float wa[kLeanPasses], wb[kLeanPasses], ga[kLeanPasses], gb[kLeanPasses], At[kLeanPasses], dxd[kLeanPasses];
+#pragma unroll
+    for (int t = 0; t < kLeanPasses; ++t) {
+        key[t] = -1; rank[t] = 0;
+        wa[t] = wb[t] = ga[t] = gb[t] = At[t] = dxd[t] = 0.f;
+        if (t < passes) {   // block-uniform
+            const int ul = t * UPP + warp * UPW + g1;
+            const bool on = lc.live && ul < Qc;
+            const Decoded d = decode<FUSED, LPA>(a, lc, raw[t], on);
+            if (on) {
+                float xa = d.w0, xb = d.w1, sa = d.s0, sb = d.s1;
+                if (d.r1 == d.r0) { xa += xb; sa += sb; xb = 0.f; sb = 0.f; }   // one row only
+                const float at = d.A * lc.tf;
+                wa[t] = xa; wb[t] = xb; ga[t] = sa * at; gb[t] = sb * at; At[t] = d.A; dxd[t] = d.dxdoff;
+                if (xa != 0.f || xb != 0.f || sa != 0.f || sb != 0.f) {
+                    key[t] = d.r0;
+                    rank[t] = atomicAdd(&start[d.r0], (xb != 0.f || sb != 0.f) ? 0x10001 : 1) & 0xffff;
+                }
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- exclusive prefix over the (even-padded) histogram + list of occupied rows ----
+    {
+        const int B = (a.S + kLeanThreads - 1) / kLeanThreads;
+        const int i0 = min(tid * B, a.S), i1 = min(i0 + B, a.S);
+        int packed = 0;   // padded count in the low 16 bits, occupied rows in the high 16 (both <= 2048)
+        for (int i = i0; i < i1; ++i) {
+            const int c = start[i] & 0xffff;
+            packed += ((c + 1) & ~1) + (c > 0 ? 65536 : 0);
+        }
+        int incl = packed;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int t = __shfl_up_sync(kFull, incl, off);
+            if (lane >= off) incl += t;
+        }
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        int prev = 0;
+        for (int w = 0; w < warp; ++w) prev += wsum[w];
+        const int run = prev + incl - packed;
+        int pos = run & 0xffff, rpos = run >> 16;
+        for (int i = i0; i < i1; ++i) {
+            const int v = start[i];
+            const int c = v & 0xffff;
+            start[i] = pos;
+            if (c > 0) {
+                rows[rpos++] = i | ((v >> 16) != 0 ? (1 << kRowFlagShift) : 0);
+                if (c & 1) ent[pos + c] = make_int4(QS, 0, 0, 0);
+                pos += (c + 1) & ~1;
+            }
+        }
+        if (tid == kLeanThreads - 1) {
+            const int tot = prev + incl;
+            start[a.S] = tot & 0xffff;
+            n_active_s = tot >> 16;
+        }
+    }
+    __syncthreads();
+
+    // ---- scatter samples into row order ----
+#pragma unroll
+    for (int t = 0; t < kLeanPasses; ++t) {
+        if (key[t] >= 0) {
+            const int ul = t * UPP + warp * UPW + g1;
+            ent[start[key[t]] + rank[t]] = make_int4((ul * LPA + j1) | (ul << 16), __float_as_int(At[t] * wa[t]),
+                                                     __float_as_int(At[t] * wb[t]), 0);
+        }
+    }
+    cp_async_commit_wait_all();
+    __syncthreads();
+
+    // ---- one lane group per occupied row ----
+    {
+        const int n_active = n_active_s;
+        const int gid = tid / LPG, j = lane % LPG;
+        const VT *vslice = static_cast<const VT *>(a.value) + (size_t)n * a.S * MD + m * a.D + j * CH;
+        float *gslice = a.gv_acc + (size_t)n * a.S * MD + m * a.D + j * CH;
+        const unsigned char *glane = Gs + j * 16;
+        float *dots_f = reinterpret_cast<float *>(dots);
+        for (int ri0 = 0; ri0 < n_active; ri0 += NG) {
+            const int ri = ri0 + gid;
+            const bool valid = ri < n_active;
+            const int rr = valid ? rows[ri] : 0;
+            const int r = rr & ((1 << kRowFlagShift) - 1);
+            const bool has1 = (rr >> kRowFlagShift) != 0;
+            const int beg = valid ? start[r] : 0;
+            const int end = valid ? start[r + 1] : 0;
+            float v0[NF], v1[NF], acc0[NF], acc1[NF];
+#pragma unroll
+            for (int k = 0; k < NF; ++k) v0[k] = v1[k] = acc0[k] = acc1[k] = 0.f;
+            if (valid) IO::load_gmem(vslice + r * MD, v0);
+            if (has1) IO::load_gmem(vslice + (r + 1) * MD, v1);
+            const int maxcnt = __reduce_max_sync(kFull, end - beg);
+            for (int t = 0; t < maxcnt; t += 2) {
+                const int tk = beg + t < end ? beg + t : 2 * QS;
+                const int4 e0 = ent[tk];
+                const int4 e1 = ent[beg + t < end ? tk + 1 : tk];
+                float gq0[NF], gq1[NF];
+                IO::load_smem(glane + (e0.x >> 16) * rb, gq0);
+                IO::load_smem(glane + (e1.x >> 16) * rb, gq1);
+                axpy<NF>(acc0, __int_as_float(e0.y), gq0);
+                axpy<NF>(acc1, __int_as_float(e0.z), gq0);
+                axpy<NF>(acc0, __int_as_float(e1.y), gq1);
+                axpy<NF>(acc1, __int_as_float(e1.z), gq1);
+                float p[4];
+                p[0] = dot<NF>(gq0, v0);
+                p[1] = dot<NF>(gq0, v1);
+                p[2] = dot<NF>(gq1, v0);
+                p[3] = dot<NF>(gq1, v1);
+                reduce_nv<LPG, 4>(p, j);
+                if (LPG >= 4) {
+                    constexpr int LPV = LPG / 4;   // lanes per value
+                    const int vi = j / LPV;
+                    if (j % LPV == 0) dots_f[2 * ((vi < 2 ? e0.x : e1.x) & 0xffff) + (vi & 1)] = p[0];
+                }
+            }
+            if (valid) {
+#pragma unroll
+                for (int c = 0; c < NCH; ++c)
+#pragma unroll
+                    for (int k = 0; k < CH; k += 4)
+                        red_add_v4(gslice + r * MD + c * LPG * CH + k, acc0[c * CH + k], acc0[c * CH + k + 1],
+                                   acc0[c * CH + k + 2], acc0[c * CH + k + 3]);
+            }
+            if (has1) {
+#pragma unroll
+                for (int c = 0; c < NCH; ++c)
+#pragma unroll
+                    for (int k = 0; k < CH; k += 4)
+                        red_add_v4(gslice + (r + 1) * MD + c * LPG * CH + k, acc1[c * CH + k], acc1[c * CH + k + 1],
+                                   acc1[c * CH + k + 2], acc1[c * CH + k + 3]);
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- per-sample gradients (everything but the two dot products is still in registers) ----
+    {
+        const bool p_pow2 = (a.P & (a.P - 1)) == 0 && a.P <= LPA;
+#pragma unroll
+        for (int t = 0; t < kLeanPasses; ++t) {
+            if (t < passes) {   // block-uniform
+                const int ul = t * UPP + warp * UPW + g1;
+                const bool on = lc.live && ul < Qc;
+                const int nq = n * a.Lq + q0 + ul;
+                const int sidx = (nq * a.M + m) * a.LP + j1;
+                float2 pd = make_float2(0.f, 0.f);
+                if (key[t] >= 0) pd = dots[ul * LPA + j1];
+                const float gat = wa[t] * pd.x + wb[t] * pd.y;   // d out / d attention weight
+                const float gx = ga[t] * pd.x + gb[t] * pd.y;    // d out / d location
+                if (!FUSED) {
+                    if (on) {
+                        a.grad_attn[sidx] = gat;
+                        // dummy y (= 0.5 on an H = 1 level): BORDER clamps it, gradient exactly 0; ZEROS keeps the
+                        // row-0 weight 1 - |y*H - 0.5| whose slope the reference kernel reports (cuh:159)
+                        const float gy = a.pad_mode == MSDA_PAD_ZEROS ? -At[t] * gat : 0.f;
+                        *reinterpret_cast<float2 *>(a.grad_loc + 2 * sidx) = make_float2(gx, gy);
+                    }
+                } else {
+                    // softmax Jacobian: g_logit_s = A_s * (ga_s - sum_t A_t ga_t)
+                    const float dotsum = group_sum<LPA>(At[t] * gat);
+                    if (on) {
+                        a.grad_offs[sidx] = gx * dxd[t];
+                        a.grad_logits[sidx] = At[t] * (gat - dotsum);
+                    }
+                    if (a.grad_ref != nullptr) {
+                        float r0g = on ? gx : 0.f;   // d(loc)/d(ref0) = 1
+                        float r1g = 0.f;             // d(loc)/d(ref1) = off * 0.5 / P
+                        if (a.R == 2 && on) r1g = gx * raw[t].x * (0.5f * a.invP);
+                        if (p_pow2) {   // the P lanes of one level are contiguous and P-aligned
+                            for (int off = a.P >> 1; off >= 1; off >>= 1) {
+                                r0g += __shfl_xor_sync(kFull, r0g, off);
+                                r1g += __shfl_xor_sync(kFull, r1g, off);
+                            }
+                            if (on && (j1 & (a.P - 1)) == 0) {
+                                float *gp = a.grad_ref + (nq * a.L + lc.l) * a.R;
+                                atomicAdd(gp, r0g);
+                                if (a.R == 2) atomicAdd(gp + 1, r1g);
+                            }
+                        } else if (on) {
+                            float *gp = a.grad_ref + (nq * a.L + lc.l) * a.R;
+                            atomicAdd(gp, r0g);
+                            if (a.R == 2) atomicAdd(gp + 1, r1g);
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
+}  // namespace msda
