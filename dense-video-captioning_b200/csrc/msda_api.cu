@@ -232,14 +232,14 @@ template <bool FUSED, bool BWD> int launch_tile(const TileArgs &a, const TilePla
 
 struct LeanPlan {
     bool ok;
-    int lpg, nch, lpa, Q, chunks, win_rows;
+    int lpg, nch, lpa, Q, chunks, win_rows, gridK;
     size_t smem;
 };
 
 LeanPlan lean_plan(const Dims &d, int dtype, bool backward)
 {
     static const int use_lean = env_int("MSDA_LEAN", 1);
-    static const int win_kb = env_int("MSDA_WIN_KB", 64);
+    static const int win_kb = env_int("MSDA_WIN_KB", 32);
     static const int passes_env = env_int("MSDA_PASSES", 0);
     LeanPlan p{};
     if (!use_lean || dtype == MSDA_F64) return p;
@@ -260,6 +260,12 @@ LeanPlan lean_plan(const Dims &d, int dtype, bool backward)
     if (passes_env > 0 && passes_env <= kLeanPasses) passes = passes_env;
     p.Q = upp * passes;
     p.chunks = (d.Lq + p.Q - 1) / p.Q;
+    // self-attention (the queries are the rows of the level pyramid): tile by time span, see tile_queries()
+    static const int use_grid = env_int("MSDA_GRID", 1);
+    if (use_grid && d.Lq == d.S && d.L > 1 && d.S < 65536 && p.Q >= 4 * d.L) {
+        p.gridK = (d.S + (p.Q - d.L) - 1) / (p.Q - d.L);   // sum_l ceil(T_l / K) <= S / K + L <= Q
+        p.chunks = p.gridK;
+    }
     if (backward) {
         p.smem = bwd_lean_smem_bytes(p.Q, p.lpa, d.S, rb);
         if (p.smem > kMaxDynSmem) return p;
@@ -285,6 +291,7 @@ void fill_lean_args(TileArgs &a, const Dims &d, const LeanPlan &p, int pad_mode)
     a.Q = p.Q;
     a.chunks = p.chunks;
     a.win_rows = p.win_rows;
+    a.gridK = p.gridK;
 }
 
 template <typename VT, int LPG, int NCH, int LPA, bool FUSED, bool BWD>

@@ -37,6 +37,71 @@ __device__ __forceinline__ LaneLevel lane_level(const TileArgs &a, int j)
     return c;
 }
 
+// ---- tiles ------------------------------------------------------------------------------------------
+// gridK == 0: tile k = the Q consecutive queries [k*Q, k*Q + Q).
+// gridK  > 0 (self-attention, Lq == S: the queries ARE the rows of the level pyramid,
+//            pdvc/deformable_transformer.py:198-208): tile k takes from EVERY level the rows whose position
+//            p satisfies k <= p*K/T_l < k+1, i.e. all queries of one time span.  Their samples then fall into
+//            one short row window per level (span + offsets) instead of Q/T_l of the whole pyramid, so the
+//            window always fits in shared memory.  Pure scheduling: results do not depend on it.
+struct TileRun {
+    int q_first;   // first query (= slice row) of this level's run
+    int count;
+};
+
+__device__ __forceinline__ void tile_runs_init(const TileArgs &a, int k, TileRun *runs)
+{
+    const int l = threadIdx.x;
+    if (l < a.L) {
+        const unsigned T = (unsigned)__ldg(a.shapes + (a.shapes_stride == 2 ? 2 * l + 1 : l));
+        const unsigned K = (unsigned)a.gridK;
+        const unsigned p0 = ((unsigned)k * T + K - 1) / K;          // S < 65536: no overflow
+        const unsigned p1 = min(T, ((unsigned)(k + 1) * T + K - 1) / K);
+        runs[l].q_first = (int)__ldg(a.lsi + l) + (int)p0;
+        runs[l].count = p1 > p0 ? (int)(p1 - p0) : 0;
+    }
+}
+
+// queries of this thread's NU units (-1: none) and the tile's query count; call after the runs are visible
+template <int NU>
+__device__ __forceinline__ int tile_queries(const TileArgs &a, int k, const TileRun *runs, const int (&ul)[NU], int (&q)[NU])
+{
+    if (a.gridK == 0) {
+        const int q0 = k * a.Q;
+        const int Qc = min(a.Q, a.Lq - q0);
+#pragma unroll
+        for (int i = 0; i < NU; ++i) q[i] = ul[i] < Qc ? q0 + ul[i] : -1;
+        return Qc;
+    }
+#pragma unroll
+    for (int i = 0; i < NU; ++i) q[i] = -1;
+    int off = 0;
+    for (int l = 0; l < a.L; ++l) {
+        const TileRun r = runs[l];
+        const int cnt = min(r.count, a.Q - off);   // never clips when sum(T_l) == Lq (host picks K for that)
+#pragma unroll
+        for (int i = 0; i < NU; ++i) {
+            const int rel = ul[i] - off;
+            if (rel >= 0 && rel < cnt) q[i] = r.q_first + rel;
+        }
+        off += cnt;
+    }
+    return off;
+}
+
+// per-level [lo, hi] row range: warp-aggregated (REDUX over the lanes of equal level), then one shared atomic
+// per level and warp instead of one per lane
+__device__ __forceinline__ void window_update(int *win_lo, int *win_hi, int level, int lo, int hi)
+{
+    const unsigned peers = __match_any_sync(kFull, level);
+    const int wlo = __reduce_min_sync(peers, lo);
+    const int whi = __reduce_max_sync(peers, hi);
+    if ((threadIdx.x & 31) == __ffs(peers) - 1 && whi >= 0) {
+        atomicMin(&win_lo[level], wlo);
+        atomicMax(&win_hi[level], whi);
+    }
+}
+
 // raw per-sample inputs (issued for all passes before anything is consumed)
 struct RawSample {
     float x;   // fused: offset            unfused: location
@@ -157,15 +222,16 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
     constexpr int G = 32 / LPG;     // units per warp in the gather phase
     constexpr int UPW = 32 / LPA;   // units per warp in the decode phase
     constexpr int UPP = kLeanWarps * UPW;
+    constexpr int QMAX = UPP * kLeanPasses;
     extern __shared__ __align__(128) unsigned char dsm[];
     __shared__ int win_lo[kMaxLevels], win_hi[kMaxLevels], win_base[kMaxLevels];
+    __shared__ TileRun runs[kMaxLevels];
+    __shared__ int uq[QMAX];   // query of every unit of the tile
     __shared__ unsigned long long mbar;
     __shared__ int win_ok;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int n = blockIdx.z, m = blockIdx.y;
-    const int q0 = blockIdx.x * a.Q;
-    const int Qc = min(a.Q, a.Lq - q0);
     const int MD = a.M * a.D;
     constexpr int rb = LPG * NCH * 16;   // bytes per row of one head (= D * sizeof(VT))
     int4 *recs = reinterpret_cast<int4 *>(dsm);
@@ -173,20 +239,25 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
 
     if (tid < a.L) { win_lo[tid] = INT_MAX; win_hi[tid] = -1; }
     if (tid == 0) mbar_init(&mbar, 1);
+    if (a.gridK) tile_runs_init(a, blockIdx.x, runs);
+    __syncthreads();   // win_lo / win_hi / mbar / runs initialised
 
     // ---- decode: lane (g, j) handles sample j of units warp*UPW + g + t*UPP, t < passes ----
     const int g1 = lane / LPA, j1 = lane % LPA;
     const LaneLevel lc = lane_level(a, j1);
+    int ulv[kLeanPasses], qv[kLeanPasses];
+#pragma unroll
+    for (int t = 0; t < kLeanPasses; ++t) ulv[t] = t * UPP + warp * UPW + g1;
+    const int Qc = tile_queries<kLeanPasses>(a, blockIdx.x, runs, ulv, qv);
     const int passes = (Qc + UPP - 1) / UPP;
     RawSample raw[kLeanPasses];
 #pragma unroll
     for (int t = 0; t < kLeanPasses; ++t) {
-        const int ul = t * UPP + warp * UPW + g1;
-        const bool on = lc.live && ul < Qc;
-        const int nq = n * a.Lq + q0 + ul;
+        const bool on = lc.live && qv[t] >= 0;
+        const int nq = n * a.Lq + (qv[t] >= 0 ? qv[t] : 0);
         raw[t] = load_raw<FUSED>(a, lc, nq, (nq * a.M + m) * a.LP + j1, on);
+        if (j1 == 0 && ulv[t] < a.Q) uq[ulv[t]] = qv[t];
     }
-    __syncthreads();   // win_lo / win_hi / mbar initialised
     int r0[kLeanPasses], r1[kLeanPasses];
     float c0[kLeanPasses], c1[kLeanPasses];
     int lo = INT_MAX, hi = -1;
@@ -195,8 +266,7 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
         r0[t] = r1[t] = -1;
         c0[t] = c1[t] = 0.f;
         if (t < passes) {   // block-uniform
-            const int ul = t * UPP + warp * UPW + g1;
-            const bool on = lc.live && ul < Qc;
+            const bool on = lc.live && qv[t] >= 0;
             const Decoded d = decode<FUSED, LPA>(a, lc, raw[t], on);
             const float k0 = d.A * d.w0, k1 = d.A * d.w1;
             if (on && (k0 != 0.f || k1 != 0.f)) {
@@ -206,7 +276,7 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
             }
         }
     }
-    if (hi >= 0) { atomicMin(&win_lo[lc.l], lo); atomicMax(&win_hi[lc.l], hi); }
+    window_update(win_lo, win_hi, lc.l, lo, hi);
     __syncthreads();
     if (tid == 0) {
         int tot = 0;
@@ -231,11 +301,10 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
         const int scale = staged ? rb : MD;
 #pragma unroll
         for (int t = 0; t < kLeanPasses; ++t) {
-            const int ul = t * UPP + warp * UPW + g1;
-            if (t < passes && ul < Qc) {
+            if (t < passes && ulv[t] < Qc) {
                 const bool livet = r0[t] >= 0;
-                recs[ul * LPA + j1] = make_int4(livet ? (base + r0[t]) * scale : 0, livet ? (base + r1[t]) * scale : 0,
-                                                __float_as_int(c0[t]), __float_as_int(c1[t]));
+                recs[ulv[t] * LPA + j1] = make_int4(livet ? (base + r0[t]) * scale : 0, livet ? (base + r1[t]) * scale : 0,
+                                                    __float_as_int(c0[t]), __float_as_int(c1[t]));
             }
         }
     }
@@ -280,7 +349,7 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
                     }
                 }
             }
-            if (active) IO::store_gmem(out + (size_t)((n * a.Lq + q0 + ul) * a.M + m) * a.D + j * CH, acc);
+            if (active) IO::store_gmem(out + (size_t)((n * a.Lq + uq[ul]) * a.M + m) * a.D + j * CH, acc);
         }
     }
 }
@@ -290,9 +359,8 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
 // backward.  grid = (chunks, M, N).  Dynamic shared memory (QS = Q * LPA sample slots):
 //   Gs    Q x D VT          grad_out rows of the chunk (this head)
 //   ent   (2*QS + 2) int4   samples in value-row order, every row's run padded to an even length:
-//                           {slot | unit << 16, A*wa, A*wb, -};  ent[2*QS] is a permanent no-op entry
+//                           {slot | unit << 16, A*wa, A*wb, row | second_tap << 30};  ent[2*QS] is a permanent no-op entry
 //   dots  (QS + 1) float2   {G.V[r], G.V[r+1]} per sample slot (+1 sink for the no-op entries)
-//   rows  QS int            occupied rows: r | needs_row_r+1 << 30
 //   start (S + 1) int       histogram of first rows -> start of each row's run in ent
 // ---------------------------------------------------------------------------------------------
 constexpr int kRowFlagShift = 30;
@@ -300,7 +368,7 @@ constexpr int kRowFlagShift = 30;
 __host__ __device__ inline size_t bwd_lean_smem_bytes(int Q, int LPA, int S, int rb)
 {
     const size_t QS = (size_t)Q * LPA;
-    return (size_t)Q * rb + (2 * QS + 2) * 16 + (QS + 1 + 1) * 8 + QS * 4 + ((size_t)S + 1 + 3) / 4 * 16;
+    return (size_t)Q * rb + (2 * QS + 2) * 16 + (QS + 1 + 1) * 8 + ((size_t)S + 1 + 3) / 4 * 16;
 }
 
 template <typename VT, int LPG, int NCH, int LPA, bool FUSED>
@@ -312,58 +380,57 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
     constexpr int NG = kLeanThreads / LPG;   // row groups per CTA
     constexpr int UPW = 32 / LPA;
     constexpr int UPP = kLeanWarps * UPW;
+    constexpr int QMAX = UPP * kLeanPasses;
     constexpr int rb = LPG * NCH * 16;
     extern __shared__ __align__(128) unsigned char dsm[];
     __shared__ int wsum[kLeanWarps];
-    __shared__ int n_active_s;
+    __shared__ int n_ent_s;
+    __shared__ int win_lo[kMaxLevels], win_hi[kMaxLevels];
+    __shared__ TileRun runs[kMaxLevels];
+    __shared__ int uq[QMAX];
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int n = blockIdx.z, m = blockIdx.y;
-    const int q0 = blockIdx.x * a.Q;
-    const int Qc = min(a.Q, a.Lq - q0);
     const int MD = a.M * a.D;
     const int QS = a.Q * LPA;
     unsigned char *Gs = dsm;
     int4 *ent = reinterpret_cast<int4 *>(Gs + (size_t)a.Q * rb);
     float2 *dots = reinterpret_cast<float2 *>(ent + 2 * QS + 2);
-    int *rows = reinterpret_cast<int *>(dots + QS + 2);
-    int *start = rows + QS;
+    int *start = reinterpret_cast<int *>(dots + QS + 2);
 
-    // ---- raw inputs of this lane's samples, grad_out rows (async), histogram reset ----
+    if (tid < a.L) { win_lo[tid] = INT_MAX; win_hi[tid] = -1; }
+    if (a.gridK) tile_runs_init(a, blockIdx.x, runs);
+    if (tid == 0) ent[2 * QS] = make_int4(QS, 0, 0, 0);   // no-op entry: unit 0, zero weights, sink slot
+    __syncthreads();
+
+    // ---- raw inputs of this lane's samples ----
     const int g1 = lane / LPA, j1 = lane % LPA;
     const LaneLevel lc = lane_level(a, j1);
+    int ulv[kLeanPasses], qv[kLeanPasses];
+#pragma unroll
+    for (int t = 0; t < kLeanPasses; ++t) ulv[t] = t * UPP + warp * UPW + g1;
+    const int Qc = tile_queries<kLeanPasses>(a, blockIdx.x, runs, ulv, qv);
     const int passes = (Qc + UPP - 1) / UPP;
     RawSample raw[kLeanPasses];
 #pragma unroll
     for (int t = 0; t < kLeanPasses; ++t) {
-        const int ul = t * UPP + warp * UPW + g1;
-        const bool on = lc.live && ul < Qc;
-        const int nq = n * a.Lq + q0 + ul;
+        const bool on = lc.live && qv[t] >= 0;
+        const int nq = n * a.Lq + (qv[t] >= 0 ? qv[t] : 0);
         raw[t] = load_raw<FUSED>(a, lc, nq, (nq * a.M + m) * a.LP + j1, on);
+        if (j1 == 0 && ulv[t] < a.Q) uq[ulv[t]] = qv[t];
     }
-    {
-        const unsigned char *gsrc =
-            static_cast<const unsigned char *>(a.grad_out) + ((size_t)(n * a.Lq + q0) * a.M + m) * rb;
-        constexpr int VPR = rb / 16;   // 16-byte vectors per row
-        for (int v = tid; v < Qc * VPR; v += kLeanThreads) {
-            const int ul = v / VPR, jj = v % VPR;
-            cp_async16(Gs + ul * rb + jj * 16, gsrc + (size_t)ul * a.M * rb + jj * 16);
-        }
-    }
-    for (int i = tid; i <= a.S; i += kLeanThreads) start[i] = 0;
-    if (tid == 0) ent[2 * QS] = make_int4(QS, 0, 0, 0);   // no-op entry: unit 0, zero weights, sink slot
-    __syncthreads();
 
-    // ---- decode + histogram of first rows ----
+    // ---- decode; per-level range of first rows ----
     int key[kLeanPasses], rank[kLeanPasses];
     float wa[kLeanPasses], wb[kLeanPasses], ga[kLeanPasses], gb[kLeanPasses], At[kLeanPasses], dxd[kLeanPasses];
+    bool two[kLeanPasses];
+    int lo = INT_MAX, hi = -1;
 #pragma unroll
     for (int t = 0; t < kLeanPasses; ++t) {
-        key[t] = -1; rank[t] = 0;
+        key[t] = -1; rank[t] = 0; two[t] = false;
         wa[t] = wb[t] = ga[t] = gb[t] = At[t] = dxd[t] = 0.f;
         if (t < passes) {   // block-uniform
-            const int ul = t * UPP + warp * UPW + g1;
-            const bool on = lc.live && ul < Qc;
+            const bool on = lc.live && qv[t] >= 0;
             const Decoded d = decode<FUSED, LPA>(a, lc, raw[t], on);
             if (on) {
                 float xa = d.w0, xb = d.w1, sa = d.s0, sb = d.s1;
@@ -372,23 +439,49 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
                 wa[t] = xa; wb[t] = xb; ga[t] = sa * at; gb[t] = sb * at; At[t] = d.A; dxd[t] = d.dxdoff;
                 if (xa != 0.f || xb != 0.f || sa != 0.f || sb != 0.f) {
                     key[t] = d.r0;
-                    rank[t] = atomicAdd(&start[d.r0], (xb != 0.f || sb != 0.f) ? 0x10001 : 1) & 0xffff;
+                    two[t] = xb != 0.f || sb != 0.f;
+                    lo = min(lo, d.r0);
+                    hi = max(hi, d.r0);
                 }
             }
         }
     }
+    window_update(win_lo, win_hi, lc.l, lo, hi);
+    __syncthreads();   // uq, win_lo / win_hi complete
+
+    // grad_out rows of the tile (async; consumed after the sort)
+    {
+        const unsigned char *gsrc = static_cast<const unsigned char *>(a.grad_out) + ((size_t)n * a.Lq * a.M + m) * rb;
+        constexpr int VPR = rb / 16;   // 16-byte vectors per row
+        for (int v = tid; v < Qc * VPR; v += kLeanThreads) {
+            const int ul = v / VPR, jj = v % VPR;
+            cp_async16(Gs + ul * rb + jj * 16, gsrc + (size_t)uq[ul] * a.M * rb + jj * 16);
+        }
+    }
+    // compact row index of slice row r at level l: wbase_l + r; tot = rows in all level windows (<= S)
+    int tot = 0, my_base = 0;
+    for (int l = 0; l < a.L; ++l) {
+        const int wl = win_lo[l], wh = win_hi[l];
+        if (l == lc.l) my_base = tot - wl;
+        if (wh >= wl) tot += wh - wl + 1;
+    }
+    for (int i = tid; i <= tot; i += kLeanThreads) start[i] = 0;
     __syncthreads();
 
-    // ---- exclusive prefix over the (even-padded) histogram + list of occupied rows ----
+    // ---- histogram of first rows ----
+#pragma unroll
+    for (int t = 0; t < kLeanPasses; ++t) {
+        if (key[t] >= 0) rank[t] = atomicAdd(&start[my_base + key[t]], 1);
+    }
+    __syncthreads();
+
+    // ---- exclusive prefix over the (even-padded) histogram ----
     {
-        const int B = (a.S + kLeanThreads - 1) / kLeanThreads;
-        const int i0 = min(tid * B, a.S), i1 = min(i0 + B, a.S);
-        int packed = 0;   // padded count in the low 16 bits, occupied rows in the high 16 (both <= 2048)
-        for (int i = i0; i < i1; ++i) {
-            const int c = start[i] & 0xffff;
-            packed += ((c + 1) & ~1) + (c > 0 ? 65536 : 0);
-        }
-        int incl = packed;
+        const int B = (tot + kLeanThreads - 1) / kLeanThreads;
+        const int i0 = min(tid * B, tot), i1 = min(i0 + B, tot);
+        int cnt = 0;   // padded count of this thread's rows
+        for (int i = i0; i < i1; ++i) cnt += ((start[i] & 0xffff) + 1) & ~1;
+        int incl = cnt;
 #pragma unroll
         for (int off = 1; off < 32; off <<= 1) {
             const int t = __shfl_up_sync(kFull, incl, off);
@@ -398,23 +491,23 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
         __syncthreads();
         int prev = 0;
         for (int w = 0; w < warp; ++w) prev += wsum[w];
-        const int run = prev + incl - packed;
-        int pos = run & 0xffff, rpos = run >> 16;
+        int pos = prev + incl - cnt;
         for (int i = i0; i < i1; ++i) {
-            const int v = start[i];
-            const int c = v & 0xffff;
+            const int c = start[i] & 0xffff;
             start[i] = pos;
-            if (c > 0) {
-                rows[rpos++] = i | ((v >> 16) != 0 ? (1 << kRowFlagShift) : 0);
-                if (c & 1) ent[pos + c] = make_int4(QS, 0, 0, 0);
-                pos += (c + 1) & ~1;
+            if (c & 1) {   // pad the row's run to an even length with a no-op entry of the same row
+                int r = i, cum = 0;   // compact index -> slice row
+                for (int l = 0; l < a.L; ++l) {
+                    const int wl = win_lo[l], wh = win_hi[l];
+                    const int sz = wh >= wl ? wh - wl + 1 : 0;
+                    if (i >= cum && i < cum + sz) r = wl + (i - cum);
+                    cum += sz;
+                }
+                ent[pos + c] = make_int4(QS, 0, 0, r);
             }
+            pos += (c + 1) & ~1;
         }
-        if (tid == kLeanThreads - 1) {
-            const int tot = prev + incl;
-            start[a.S] = tot & 0xffff;
-            n_active_s = tot >> 16;
-        }
+        if (tid == kLeanThreads - 1) n_ent_s = prev + incl;
     }
     __syncthreads();
 
@@ -422,76 +515,89 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
 #pragma unroll
     for (int t = 0; t < kLeanPasses; ++t) {
         if (key[t] >= 0) {
-            const int ul = t * UPP + warp * UPW + g1;
-            ent[start[key[t]] + rank[t]] = make_int4((ul * LPA + j1) | (ul << 16), __float_as_int(At[t] * wa[t]),
-                                                     __float_as_int(At[t] * wb[t]), 0);
+            const int ul = ulv[t];
+            ent[start[my_base + key[t]] + rank[t]] =
+                make_int4((ul * LPA + j1) | (ul << 16), __float_as_int(At[t] * wa[t]), __float_as_int(At[t] * wb[t]),
+                          key[t] | (two[t] ? (1 << kRowFlagShift) : 0));
         }
     }
     cp_async_commit_wait_all();
     __syncthreads();
 
-    // ---- one lane group per occupied row ----
+    // ---- row-ordered sweep: every lane group takes an equal share of the (row-sorted) entry pairs ----
+    // A group keeps V[r], V[r+1] and the two grad_value accumulators of its current row in registers and
+    // flushes them with one vector reduction per row change; a row split between groups is simply reduced
+    // twice.  Balanced by construction (coarse levels have ~6x more samples per row than level 0).
     {
-        const int n_active = n_active_s;
+        const int pairs = n_ent_s >> 1;
+        const int pp = (pairs + NG - 1) / NG;   // pairs per group
         const int gid = tid / LPG, j = lane % LPG;
         const VT *vslice = static_cast<const VT *>(a.value) + (size_t)n * a.S * MD + m * a.D + j * CH;
         float *gslice = a.gv_acc + (size_t)n * a.S * MD + m * a.D + j * CH;
         const unsigned char *glane = Gs + j * 16;
         float *dots_f = reinterpret_cast<float *>(dots);
-        for (int ri0 = 0; ri0 < n_active; ri0 += NG) {
-            const int ri = ri0 + gid;
-            const bool valid = ri < n_active;
-            const int rr = valid ? rows[ri] : 0;
-            const int r = rr & ((1 << kRowFlagShift) - 1);
-            const bool has1 = (rr >> kRowFlagShift) != 0;
-            const int beg = valid ? start[r] : 0;
-            const int end = valid ? start[r + 1] : 0;
-            float v0[NF], v1[NF], acc0[NF], acc1[NF];
+        float v0[NF], v1[NF], acc0[NF], acc1[NF];
 #pragma unroll
-            for (int k = 0; k < NF; ++k) v0[k] = v1[k] = acc0[k] = acc1[k] = 0.f;
-            if (valid) IO::load_gmem(vslice + r * MD, v0);
-            if (has1) IO::load_gmem(vslice + (r + 1) * MD, v1);
-            const int maxcnt = __reduce_max_sync(kFull, end - beg);
-            for (int t = 0; t < maxcnt; t += 2) {
-                const int tk = beg + t < end ? beg + t : 2 * QS;
-                const int4 e0 = ent[tk];
-                const int4 e1 = ent[beg + t < end ? tk + 1 : tk];
-                float gq0[NF], gq1[NF];
-                IO::load_smem(glane + (e0.x >> 16) * rb, gq0);
-                IO::load_smem(glane + (e1.x >> 16) * rb, gq1);
-                axpy<NF>(acc0, __int_as_float(e0.y), gq0);
-                axpy<NF>(acc1, __int_as_float(e0.z), gq0);
-                axpy<NF>(acc0, __int_as_float(e1.y), gq1);
-                axpy<NF>(acc1, __int_as_float(e1.z), gq1);
-                float p[4];
-                p[0] = dot<NF>(gq0, v0);
-                p[1] = dot<NF>(gq0, v1);
-                p[2] = dot<NF>(gq1, v0);
-                p[3] = dot<NF>(gq1, v1);
-                reduce_nv<LPG, 4>(p, j);
-                if (LPG >= 4) {
-                    constexpr int LPV = LPG / 4;   // lanes per value
-                    const int vi = j / LPV;
-                    if (j % LPV == 0) dots_f[2 * ((vi < 2 ? e0.x : e1.x) & 0xffff) + (vi & 1)] = p[0];
+        for (int k = 0; k < NF; ++k) v0[k] = v1[k] = acc0[k] = acc1[k] = 0.f;
+        int cur = -1;
+        bool any1 = false;
+        auto flush = [&]() {
+            if (cur >= 0) {
+#pragma unroll
+                for (int c = 0; c < NCH; ++c)
+#pragma unroll
+                    for (int k = 0; k < CH; k += 4)
+                        red_add_v4(gslice + cur * MD + c * LPG * CH + k, acc0[c * CH + k], acc0[c * CH + k + 1],
+                                   acc0[c * CH + k + 2], acc0[c * CH + k + 3]);
+                if (any1) {
+#pragma unroll
+                    for (int c = 0; c < NCH; ++c)
+#pragma unroll
+                        for (int k = 0; k < CH; k += 4)
+                            red_add_v4(gslice + (cur + 1) * MD + c * LPG * CH + k, acc1[c * CH + k], acc1[c * CH + k + 1],
+                                       acc1[c * CH + k + 2], acc1[c * CH + k + 3]);
                 }
             }
-            if (valid) {
+        };
+        for (int it = 0; it < pp; ++it) {
+            const int pi = gid * pp + it;
+            const bool ok = pi < pairs;
+            const int4 e0 = ent[ok ? 2 * pi : 2 * QS];
+            const int4 e1 = ent[ok ? 2 * pi + 1 : 2 * QS];
+            const int row = ok ? (e0.w & ((1 << kRowFlagShift) - 1)) : cur;
+            const bool chg = row != cur;
+            if (__any_sync(kFull, chg)) {
+                if (chg) {
+                    flush();
+                    cur = row;
+                    any1 = false;
 #pragma unroll
-                for (int c = 0; c < NCH; ++c)
-#pragma unroll
-                    for (int k = 0; k < CH; k += 4)
-                        red_add_v4(gslice + r * MD + c * LPG * CH + k, acc0[c * CH + k], acc0[c * CH + k + 1],
-                                   acc0[c * CH + k + 2], acc0[c * CH + k + 3]);
+                    for (int k = 0; k < NF; ++k) v1[k] = acc0[k] = acc1[k] = 0.f;
+                    IO::load_gmem(vslice + row * MD, v0);
+                    if (row + 1 < a.S) IO::load_gmem(vslice + (row + 1) * MD, v1);
+                }
             }
-            if (has1) {
-#pragma unroll
-                for (int c = 0; c < NCH; ++c)
-#pragma unroll
-                    for (int k = 0; k < CH; k += 4)
-                        red_add_v4(gslice + (r + 1) * MD + c * LPG * CH + k, acc1[c * CH + k], acc1[c * CH + k + 1],
-                                   acc1[c * CH + k + 2], acc1[c * CH + k + 3]);
+            any1 = any1 || ((e0.w | e1.w) >> kRowFlagShift) != 0;
+            float gq0[NF], gq1[NF];
+            IO::load_smem(glane + (e0.x >> 16) * rb, gq0);
+            IO::load_smem(glane + (e1.x >> 16) * rb, gq1);
+            axpy<NF>(acc0, __int_as_float(e0.y), gq0);
+            axpy<NF>(acc1, __int_as_float(e0.z), gq0);
+            axpy<NF>(acc0, __int_as_float(e1.y), gq1);
+            axpy<NF>(acc1, __int_as_float(e1.z), gq1);
+            float p[4];
+            p[0] = dot<NF>(gq0, v0);
+            p[1] = dot<NF>(gq0, v1);
+            p[2] = dot<NF>(gq1, v0);
+            p[3] = dot<NF>(gq1, v1);
+            reduce_nv<LPG, 4>(p, j);
+            if (LPG >= 4) {
+                constexpr int LPV = LPG / 4;   // lanes per value
+                const int vi = j / LPV;
+                if (j % LPV == 0) dots_f[2 * ((vi < 2 ? e0.x : e1.x) & 0xffff) + (vi & 1)] = p[0];
             }
         }
+        flush();
     }
     __syncthreads();
 
@@ -501,9 +607,9 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
 #pragma unroll
         for (int t = 0; t < kLeanPasses; ++t) {
             if (t < passes) {   // block-uniform
-                const int ul = t * UPP + warp * UPW + g1;
-                const bool on = lc.live && ul < Qc;
-                const int nq = n * a.Lq + q0 + ul;
+                const int ul = ulv[t];
+                const bool on = lc.live && qv[t] >= 0;
+                const int nq = n * a.Lq + (qv[t] >= 0 ? qv[t] : 0);
                 const int sidx = (nq * a.M + m) * a.LP + j1;
                 float2 pd = make_float2(0.f, 0.f);
                 if (key[t] >= 0) pd = dots[ul * LPA + j1];

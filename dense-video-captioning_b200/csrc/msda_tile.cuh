@@ -55,6 +55,7 @@ struct TileArgs {
     int Q;         // queries per chunk
     int chunks;    // ceil(Lq / Q)
     int win_rows;  // forward: capacity of the shared-memory value window in rows (0: never stage)
+    int gridK;     // lean kernels: 0 = a tile is Q consecutive queries; K > 0 = level-grid tiling into K time spans
 };
 
 // ---- small PTX wrappers -------------------------------------------------------------------
