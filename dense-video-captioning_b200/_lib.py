@@ -10,7 +10,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libmsda_sm100.so")
+# MSDA_LIB selects another build of the same library (development: lib/libmsda_dev.so)
+LIB_PATH = os.environ.get("MSDA_LIB") or os.path.join(_HERE, "lib", "libmsda_sm100.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 F32, BF16, F64 = 0, 1, 2

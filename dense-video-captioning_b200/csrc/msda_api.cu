@@ -12,6 +12,7 @@
 #include "msda_generic.cuh"
 #include "msda_tile.cuh"
 #include "msda_lean.cuh"
+#include "msda_pipe.cuh"
 
 using namespace msda;
 
@@ -83,6 +84,9 @@ void fast_grid(int total_units, int lpg, int &grid, int &units_per_cta)
 
 template <typename VT, bool FUSED> int launch_fast_fwd(const FastArgs &a, int lpg, int grid, cudaStream_t st)
 {
+#ifdef MSDA_DEV_FAST
+    return MSDA_ERR_UNSUPPORTED;
+#else
     switch (lpg) {
         case 4: msda_fwd_fast_kernel<VT, 4, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
         case 8: msda_fwd_fast_kernel<VT, 8, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
@@ -90,10 +94,14 @@ template <typename VT, bool FUSED> int launch_fast_fwd(const FastArgs &a, int lp
         default: msda_fwd_fast_kernel<VT, 32, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
     }
     return check_launch();
+#endif
 }
 
 template <typename VT, bool FUSED> int launch_fast_bwd(const FastArgs &a, int lpg, int grid, cudaStream_t st)
 {
+#ifdef MSDA_DEV_FAST
+    return MSDA_ERR_UNSUPPORTED;
+#else
     switch (lpg) {
         case 4: msda_bwd_fast_kernel<VT, 4, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
         case 8: msda_bwd_fast_kernel<VT, 8, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
@@ -101,6 +109,7 @@ template <typename VT, bool FUSED> int launch_fast_bwd(const FastArgs &a, int lp
         default: msda_bwd_fast_kernel<VT, 32, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
     }
     return check_launch();
+#endif
 }
 
 // ---- chunked ("tile") kernels: planning ----------------------------------------------------------
@@ -208,6 +217,9 @@ int launch_tile_inst(const TileArgs &a, int grid, size_t smem, cudaStream_t st)
 template <typename VT, bool FUSED, bool BWD>
 int launch_tile_lanes(const TileArgs &a, const TilePlan &p, int grid, cudaStream_t st)
 {
+#ifdef MSDA_DEV_FAST
+    return MSDA_ERR_UNSUPPORTED;
+#else
 #define MSDA_TILE_CASE(LPG_)                                                                                  \
     case LPG_:                                                                                                \
         return p.lpa == 16 ? launch_tile_inst<VT, LPG_, 16, FUSED, BWD>(a, grid, p.smem, st)                  \
@@ -219,6 +231,7 @@ int launch_tile_lanes(const TileArgs &a, const TilePlan &p, int grid, cudaStream
         default: MSDA_TILE_CASE(32)
     }
 #undef MSDA_TILE_CASE
+#endif
 }
 
 template <bool FUSED, bool BWD> int launch_tile(const TileArgs &a, const TilePlan &p, int dtype, cudaStream_t st)
@@ -267,7 +280,14 @@ LeanPlan lean_plan(const Dims &d, int dtype, bool backward)
         p.chunks = p.gridK;
     }
     if (backward) {
-        p.smem = bwd_lean_smem_bytes(p.Q, p.lpa, d.S, rb);
+        static const int bwin_kb = env_int("MSDA_BWIN_KB", 34);
+        p.win_rows = bwin_kb * 1024 / rb;
+        if (p.win_rows > d.S + d.L) p.win_rows = d.S + d.L;
+        p.smem = bwd_lean_smem_bytes(p.Q, p.lpa, d.S, rb, p.win_rows);
+        if (p.smem > kMaxDynSmem) {   // no room for a window: gather value rows through L1
+            p.win_rows = 0;
+            p.smem = bwd_lean_smem_bytes(p.Q, p.lpa, d.S, rb, 0);
+        }
         if (p.smem > kMaxDynSmem) return p;
     } else {
         const size_t recs = (size_t)p.Q * p.lpa * sizeof(int4);
@@ -309,16 +329,36 @@ int launch_lean_inst(const TileArgs &a, const LeanPlan &p, cudaStream_t st)
     return check_launch();
 }
 
+// persistent pipelined forward (msda_pipe.cuh): 2 CTAs per SM, double-buffered records + window
+template <typename VT, int LPG, int NCH, int LPA, bool FUSED>
+int launch_pipe_inst(const TileArgs &a, const LeanPlan &p, cudaStream_t st)
+{
+    static unsigned long long done = 0;
+    if (int e = allow_big_smem(msda_fwd_pipe_kernel<VT, LPG, NCH, LPA, FUSED>, done)) return e;
+    const long long tiles = (long long)p.chunks * a.M * a.N;
+    const int grid = (int)(tiles < 2 * kNumSMs ? tiles : 2 * kNumSMs);
+    msda_fwd_pipe_kernel<VT, LPG, NCH, LPA, FUSED><<<grid, kLeanThreads, 2 * p.smem, st>>>(a);
+    return check_launch();
+}
+
 template <typename VT, bool FUSED, bool BWD> int launch_lean_shape(const TileArgs &a, const LeanPlan &p, cudaStream_t st)
 {
+    static const int use_pipe = env_int("MSDA_PIPE", 0);
+    const bool pipe = !BWD && use_pipe && 2 * p.smem <= 110 * 1024 && (long long)p.chunks * a.M * a.N < (1ll << 31);
 #define MSDA_LEAN_CASE(LPG_, NCH_)                                                                       \
-    if (p.lpg == LPG_ && p.nch == NCH_)                                                                  \
+    if (p.lpg == LPG_ && p.nch == NCH_) {                                                                \
+        if (pipe)                                                                                        \
+            return p.lpa == 16 ? launch_pipe_inst<VT, LPG_, NCH_, 16, FUSED>(a, p, st)                   \
+                               : launch_pipe_inst<VT, LPG_, NCH_, 32, FUSED>(a, p, st);                  \
         return p.lpa == 16 ? launch_lean_inst<VT, LPG_, NCH_, 16, FUSED, BWD>(a, p, st)                  \
-                           : launch_lean_inst<VT, LPG_, NCH_, 32, FUSED, BWD>(a, p, st);
+                           : launch_lean_inst<VT, LPG_, NCH_, 32, FUSED, BWD>(a, p, st);                 \
+    }
+#ifndef MSDA_DEV_FAST   // development builds instantiate the headline shape only
     MSDA_LEAN_CASE(4, 1)
     MSDA_LEAN_CASE(8, 1)
-    MSDA_LEAN_CASE(8, 2)
     MSDA_LEAN_CASE(8, 4)
+#endif
+    MSDA_LEAN_CASE(8, 2)
 #undef MSDA_LEAN_CASE
     return MSDA_ERR_UNSUPPORTED;
 }
@@ -381,6 +421,15 @@ extern "C" {
 int msda_version(void) { return MSDA_VERSION; }
 const char *msda_arch(void) { return "sm_100a"; }
 int msda_last_launch_count(void) { return g_launches; }
+#ifdef MSDA_PHASE_TIMING
+int msda_dev_phase_clocks(unsigned long long *out32, int reset)
+{
+    cudaDeviceSynchronize();
+    cudaError_t e = cudaMemcpyFromSymbol(out32, g_phase_clk, sizeof(unsigned long long) * 32);
+    if (reset) { unsigned long long z[32] = {}; cudaMemcpyToSymbol(g_phase_clk, z, sizeof(z)); }
+    return (int)e;
+}
+#endif
 
 const char *msda_error_string(int code)
 {

@@ -15,6 +15,19 @@
 
 namespace msda {
 
+// Development aid (-DMSDA_PHASE_TIMING): thread 0 of every CTA stamps clock64() at phase boundaries and adds the
+// deltas to a device array read back by msda_dev_phase_clocks().  Compiled out of the shipped library.
+#ifdef MSDA_PHASE_TIMING
+__device__ unsigned long long g_phase_clk[2][16];
+#define MSDA_PHASE_DECL unsigned long long ph_t[16]; int ph_n = 0; if (threadIdx.x == 0) ph_t[ph_n++] = clock64();
+#define MSDA_PHASE_MARK if (threadIdx.x == 0) ph_t[ph_n++] = clock64();
+#define MSDA_PHASE_FLUSH(K) if (threadIdx.x == 0) for (int i = 1; i < ph_n; ++i) atomicAdd(&g_phase_clk[K][i - 1], ph_t[i] - ph_t[i - 1]);
+#else
+#define MSDA_PHASE_DECL
+#define MSDA_PHASE_MARK
+#define MSDA_PHASE_FLUSH(K)
+#endif
+
 constexpr int kLeanThreads = 256;
 constexpr int kLeanWarps = kLeanThreads / 32;
 constexpr int kLeanPasses = 4;   // units decoded per lane group and CTA (Q = kLeanPasses * units per pass)
@@ -224,10 +237,10 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
     constexpr int UPP = kLeanWarps * UPW;
     constexpr int QMAX = UPP * kLeanPasses;
     extern __shared__ __align__(128) unsigned char dsm[];
+    MSDA_PHASE_DECL
     __shared__ int win_lo[kMaxLevels], win_hi[kMaxLevels], win_base[kMaxLevels];
     __shared__ TileRun runs[kMaxLevels];
     __shared__ int uq[QMAX];   // query of every unit of the tile
-    __shared__ unsigned long long mbar;
     __shared__ int win_ok;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -238,9 +251,9 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
     unsigned char *win = dsm + (size_t)a.Q * LPA * sizeof(int4);
 
     if (tid < a.L) { win_lo[tid] = INT_MAX; win_hi[tid] = -1; }
-    if (tid == 0) mbar_init(&mbar, 1);
     if (a.gridK) tile_runs_init(a, blockIdx.x, runs);
     __syncthreads();   // win_lo / win_hi / mbar / runs initialised
+    MSDA_PHASE_MARK
 
     // ---- decode: lane (g, j) handles sample j of units warp*UPW + g + t*UPP, t < passes ----
     const int g1 = lane / LPA, j1 = lane % LPA;
@@ -278,6 +291,7 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
     }
     window_update(win_lo, win_hi, lc.l, lo, hi);
     __syncthreads();
+    MSDA_PHASE_MARK
     if (tid == 0) {
         int tot = 0;
         for (int l = 0; l < a.L; ++l) {
@@ -286,15 +300,23 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
         }
         const int ok = (tot > 0 && tot <= a.win_rows) ? 1 : 0;
         win_ok = ok;
-        if (ok) mbar_expect_tx(&mbar, (unsigned)tot * (unsigned)rb);
     }
     __syncthreads();
+    MSDA_PHASE_MARK
     const bool staged = win_ok != 0;
     const VT *vslice = static_cast<const VT *>(a.value) + (size_t)n * a.S * MD + m * a.D;
     if (staged) {
-        for (int l = 0; l < a.L; ++l)
-            for (int r = win_lo[l] + tid; r <= win_hi[l]; r += kLeanThreads)
-                bulk_g2s(win + (win_base[l] + r) * rb, vslice + (size_t)r * MD, (unsigned)rb, &mbar);
+        // 16-byte cp.async per lane: measured 2x cheaper to issue than one 256-byte cp.async.bulk per row
+        // (profiles/r1_phases.txt); the TMA engine serialises small bulk copies
+        constexpr int VPR = rb / 16;
+        for (int l = 0; l < a.L; ++l) {
+            const int nv = (win_hi[l] - win_lo[l] + 1) * VPR;
+            for (int v = tid; v < nv; v += kLeanThreads) {
+                const int r = win_lo[l] + v / VPR, jj = v % VPR;
+                cp_async16(win + (win_base[l] + r) * rb + jj * 16,
+                           reinterpret_cast<const unsigned char *>(vslice + (size_t)r * MD) + jj * 16);
+            }
+        }
     }
     {   // final records: byte offsets into the window (staged) or element offsets into the slice
         const int base = staged ? win_base[lc.l] : 0;
@@ -308,8 +330,10 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
             }
         }
     }
+    cp_async_commit_wait_all();
     __syncthreads();
-    if (staged) mbar_wait(&mbar, 0);
+    MSDA_PHASE_MARK
+    MSDA_PHASE_MARK
 
     // ---- gather ----
     {
@@ -352,6 +376,8 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
             if (active) IO::store_gmem(out + (size_t)((n * a.Lq + uq[ul]) * a.M + m) * a.D + j * CH, acc);
         }
     }
+    MSDA_PHASE_MARK
+    MSDA_PHASE_FLUSH(0)
 }
 
 
@@ -359,16 +385,17 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
 // backward.  grid = (chunks, M, N).  Dynamic shared memory (QS = Q * LPA sample slots):
 //   Gs    Q x D VT          grad_out rows of the chunk (this head)
 //   ent   (2*QS + 2) int4   samples in value-row order, every row's run padded to an even length:
-//                           {slot | unit << 16, A*wa, A*wb, row | second_tap << 30};  ent[2*QS] is a permanent no-op entry
+//                           {sample slot | second_tap << 15 | window slot << 16, A*wa, A*wb, row};  ent[2*QS] = no-op entry
 //   dots  (QS + 1) float2   {G.V[r], G.V[r+1]} per sample slot (+1 sink for the no-op entries)
 //   start (S + 1) int       histogram of first rows -> start of each row's run in ent
+//   Vw    win_rows x D VT   value rows of the tile's level windows (falls back to global loads if they do not fit)
 // ---------------------------------------------------------------------------------------------
 constexpr int kRowFlagShift = 30;
 
-__host__ __device__ inline size_t bwd_lean_smem_bytes(int Q, int LPA, int S, int rb)
+__host__ __device__ inline size_t bwd_lean_smem_bytes(int Q, int LPA, int S, int rb, int win_rows)
 {
     const size_t QS = (size_t)Q * LPA;
-    return (size_t)Q * rb + (2 * QS + 2) * 16 + (QS + 1 + 1) * 8 + ((size_t)S + 1 + 3) / 4 * 16;
+    return (size_t)Q * rb + (2 * QS + 2) * 16 + (QS + 1 + 1) * 8 + ((size_t)S + 1 + 3) / 4 * 16 + (size_t)win_rows * rb;
 }
 
 template <typename VT, int LPG, int NCH, int LPA, bool FUSED>
@@ -383,6 +410,7 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
     constexpr int QMAX = UPP * kLeanPasses;
     constexpr int rb = LPG * NCH * 16;
     extern __shared__ __align__(128) unsigned char dsm[];
+    MSDA_PHASE_DECL
     __shared__ int wsum[kLeanWarps];
     __shared__ int n_ent_s;
     __shared__ int win_lo[kMaxLevels], win_hi[kMaxLevels];
@@ -397,11 +425,13 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
     int4 *ent = reinterpret_cast<int4 *>(Gs + (size_t)a.Q * rb);
     float2 *dots = reinterpret_cast<float2 *>(ent + 2 * QS + 2);
     int *start = reinterpret_cast<int *>(dots + QS + 2);
+    unsigned char *Vw = reinterpret_cast<unsigned char *>(start + (a.S + 1 + 3) / 4 * 4);   // value window, win_rows x rb
 
     if (tid < a.L) { win_lo[tid] = INT_MAX; win_hi[tid] = -1; }
     if (a.gridK) tile_runs_init(a, blockIdx.x, runs);
     if (tid == 0) ent[2 * QS] = make_int4(QS, 0, 0, 0);   // no-op entry: unit 0, zero weights, sink slot
     __syncthreads();
+    MSDA_PHASE_MARK
 
     // ---- raw inputs of this lane's samples ----
     const int g1 = lane / LPA, j1 = lane % LPA;
@@ -448,6 +478,7 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
     }
     window_update(win_lo, win_hi, lc.l, lo, hi);
     __syncthreads();   // uq, win_lo / win_hi complete
+    MSDA_PHASE_MARK
 
     // grad_out rows of the tile (async; consumed after the sort)
     {
@@ -466,7 +497,30 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
         if (wh >= wl) tot += wh - wl + 1;
     }
     for (int i = tid; i <= tot; i += kLeanThreads) start[i] = 0;
+    // value window: rows [lo_l, hi_l + 1] of every touched level (first rows and their second taps), cp.async
+    int vtot = 0, my_vbase = 0;
+    for (int l = 0; l < a.L; ++l) {
+        if (l == lc.l) my_vbase = vtot - win_lo[l];
+        vtot += win_hi[l] >= win_lo[l] ? win_hi[l] - win_lo[l] + 2 : 0;
+    }
+    const bool vstaged = vtot <= a.win_rows;
+    if (vstaged) {
+        constexpr int VPR = rb / 16;
+        const unsigned char *vsrc = reinterpret_cast<const unsigned char *>(static_cast<const VT *>(a.value) + (size_t)n * a.S * MD + m * a.D);
+        int cum = 0;
+        for (int l = 0; l < a.L; ++l) {
+            const int wl = win_lo[l], wh = win_hi[l];
+            if (wh < wl) continue;
+            const int nr = min(wh + 1, a.S - 1) - wl + 1;
+            for (int v = tid; v < nr * VPR; v += kLeanThreads) {
+                const int rr = v / VPR, jj = v % VPR;
+                cp_async16(Vw + (cum + rr) * rb + jj * 16, vsrc + (size_t)(wl + rr) * MD * sizeof(VT) + jj * 16);
+            }
+            cum += wh - wl + 2;
+        }
+    }
     __syncthreads();
+    MSDA_PHASE_MARK
 
     // ---- histogram of first rows ----
 #pragma unroll
@@ -474,6 +528,7 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
         if (key[t] >= 0) rank[t] = atomicAdd(&start[my_base + key[t]], 1);
     }
     __syncthreads();
+    MSDA_PHASE_MARK
 
     // ---- exclusive prefix over the (even-padded) histogram ----
     {
@@ -489,6 +544,7 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
         }
         if (lane == 31) wsum[warp] = incl;
         __syncthreads();
+    MSDA_PHASE_MARK
         int prev = 0;
         for (int w = 0; w < warp; ++w) prev += wsum[w];
         int pos = prev + incl - cnt;
@@ -510,6 +566,7 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
         if (tid == kLeanThreads - 1) n_ent_s = prev + incl;
     }
     __syncthreads();
+    MSDA_PHASE_MARK
 
     // ---- scatter samples into row order ----
 #pragma unroll
@@ -517,12 +574,13 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
         if (key[t] >= 0) {
             const int ul = ulv[t];
             ent[start[my_base + key[t]] + rank[t]] =
-                make_int4((ul * LPA + j1) | (ul << 16), __float_as_int(At[t] * wa[t]), __float_as_int(At[t] * wb[t]),
-                          key[t] | (two[t] ? (1 << kRowFlagShift) : 0));
+                make_int4((ul * LPA + j1) | (two[t] ? 0x8000 : 0) | ((my_vbase + key[t]) << 16), __float_as_int(At[t] * wa[t]),
+                          __float_as_int(At[t] * wb[t]), key[t]);
         }
     }
     cp_async_commit_wait_all();
     __syncthreads();
+    MSDA_PHASE_MARK
 
     // ---- row-ordered sweep: every lane group takes an equal share of the (row-sorted) entry pairs ----
     // A group keeps V[r], V[r+1] and the two grad_value accumulators of its current row in registers and
@@ -564,7 +622,7 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
             const bool ok = pi < pairs;
             const int4 e0 = ent[ok ? 2 * pi : 2 * QS];
             const int4 e1 = ent[ok ? 2 * pi + 1 : 2 * QS];
-            const int row = ok ? (e0.w & ((1 << kRowFlagShift) - 1)) : cur;
+            const int row = ok ? e0.w : cur;
             const bool chg = row != cur;
             if (__any_sync(kFull, chg)) {
                 if (chg) {
@@ -573,14 +631,23 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
                     any1 = false;
 #pragma unroll
                     for (int k = 0; k < NF; ++k) v1[k] = acc0[k] = acc1[k] = 0.f;
-                    IO::load_gmem(vslice + row * MD, v0);
-                    if (row + 1 < a.S) IO::load_gmem(vslice + (row + 1) * MD, v1);
+                    if (vstaged) {
+                        const int slot = (int)((unsigned)e0.x >> 16);
+                        IO::load_smem(Vw + slot * rb + j * 16, v0);
+                        if (row + 1 < a.S) IO::load_smem(Vw + (slot + 1) * rb + j * 16, v1);
+                    } else {
+                        IO::load_gmem(vslice + row * MD, v0);
+                        if (row + 1 < a.S) IO::load_gmem(vslice + (row + 1) * MD, v1);
+                    }
                 }
             }
-            any1 = any1 || ((e0.w | e1.w) >> kRowFlagShift) != 0;
+            any1 = any1 || ((e0.x | e1.x) & 0x8000) != 0;
             float gq0[NF], gq1[NF];
-            IO::load_smem(glane + (e0.x >> 16) * rb, gq0);
-            IO::load_smem(glane + (e1.x >> 16) * rb, gq1);
+            int u0 = (e0.x & 0x7fff) / LPA, u1 = (e1.x & 0x7fff) / LPA;   // no-op entries (slot QS) read unit 0
+            u0 = u0 < a.Q ? u0 : 0;
+            u1 = u1 < a.Q ? u1 : 0;
+            IO::load_smem(glane + u0 * rb, gq0);
+            IO::load_smem(glane + u1 * rb, gq1);
             axpy<NF>(acc0, __int_as_float(e0.y), gq0);
             axpy<NF>(acc1, __int_as_float(e0.z), gq0);
             axpy<NF>(acc0, __int_as_float(e1.y), gq1);
@@ -594,12 +661,13 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
             if (LPG >= 4) {
                 constexpr int LPV = LPG / 4;   // lanes per value
                 const int vi = j / LPV;
-                if (j % LPV == 0) dots_f[2 * ((vi < 2 ? e0.x : e1.x) & 0xffff) + (vi & 1)] = p[0];
+                if (j % LPV == 0) dots_f[2 * ((vi < 2 ? e0.x : e1.x) & 0x7fff) + (vi & 1)] = p[0];
             }
         }
         flush();
     }
     __syncthreads();
+    MSDA_PHASE_MARK
 
     // ---- per-sample gradients (everything but the two dot products is still in registers) ----
     {
@@ -654,6 +722,8 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
             }
         }
     }
+    MSDA_PHASE_MARK
+    MSDA_PHASE_FLUSH(1)
 }
 
 }  // namespace msda
