@@ -28,6 +28,9 @@ __device__ unsigned long long g_phase_clk[2][16];
 #define MSDA_PHASE_FLUSH(K)
 #endif
 
+#ifndef MSDA_BWD_MINB
+#define MSDA_BWD_MINB 2
+#endif
 constexpr int kLeanThreads = 256;
 constexpr int kLeanWarps = kLeanThreads / 32;
 constexpr int kLeanPasses = 4;   // units decoded per lane group and CTA (Q = kLeanPasses * units per pass)
@@ -101,6 +104,11 @@ __device__ __forceinline__ int tile_queries(const TileArgs &a, int k, const Tile
     }
     return off;
 }
+
+// Record slot swizzle: the lane groups of a warp read the records of consecutive units at the same sample
+// index; unit records are 16 * LPA bytes apart (same banks), so sample s of unit u lives in slot s ^ 2*(u & 3)
+// -- four consecutive units then hit four different 16-byte bank groups (one wavefront instead of four).
+__device__ __forceinline__ int rec_swizzle(int unit) { return (unit & 3) << 1; }
 
 // per-level [lo, hi] row range: warp-aggregated (REDUX over the lanes of equal level), then one shared atomic
 // per level and warp instead of one per lane
@@ -325,7 +333,7 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
         for (int t = 0; t < kLeanPasses; ++t) {
             if (t < passes && ulv[t] < Qc) {
                 const bool livet = r0[t] >= 0;
-                recs[ulv[t] * LPA + j1] = make_int4(livet ? (base + r0[t]) * scale : 0, livet ? (base + r1[t]) * scale : 0,
+                recs[ulv[t] * LPA + (j1 ^ rec_swizzle(ulv[t]))] = make_int4(livet ? (base + r0[t]) * scale : 0, livet ? (base + r1[t]) * scale : 0,
                                                     __float_as_int(c0[t]), __float_as_int(c1[t]));
             }
         }
@@ -346,13 +354,14 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
             const int ul = ul0 + g;
             const bool active = ul < Qc;
             const int4 *rp = recs + (active ? ul : 0) * LPA;
+            const int sw = rec_swizzle(active ? ul : 0);
             float acc[NF];
 #pragma unroll
             for (int k = 0; k < NF; ++k) acc[k] = 0.f;
             for (int s = 0; s < LP4; s += 4) {
                 int4 r[4];
 #pragma unroll
-                for (int b = 0; b < 4; ++b) r[b] = rp[s + b];
+                for (int b = 0; b < 4; ++b) r[b] = rp[(s + b) ^ sw];
                 if (staged) {
 #pragma unroll
                     for (int b = 0; b < 4; ++b) {
@@ -399,7 +408,7 @@ __host__ __device__ inline size_t bwd_lean_smem_bytes(int Q, int LPA, int S, int
 }
 
 template <typename VT, int LPG, int NCH, int LPA, bool FUSED>
-__global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const TileArgs a)
+__global__ void __launch_bounds__(kLeanThreads, MSDA_BWD_MINB) msda_bwd_lean_kernel(const TileArgs a)
 {
     using IO = RowIO<VT, LPG, NCH>;
     constexpr int CH = Vec16<VT>::CH;
@@ -588,7 +597,9 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_bwd_lean_kernel(const Ti
     // twice.  Balanced by construction (coarse levels have ~6x more samples per row than level 0).
     {
         const int pairs = n_ent_s >> 1;
-        const int pp = (pairs + NG - 1) / NG;   // pairs per group
+        // pairs per group, rounded up to 1 (mod 4): the four groups of a warp then read entries 32 (mod 128)
+        // bytes apart -- conflict-free LDS.128 of the entry pairs
+        const int pp = (((pairs + NG - 1) / NG + 2) & ~3) + 1;
         const int gid = tid / LPG, j = lane % LPG;
         const VT *vslice = static_cast<const VT *>(a.value) + (size_t)n * a.S * MD + m * a.D + j * CH;
         float *gslice = a.gv_acc + (size_t)n * a.S * MD + m * a.D + j * CH;

@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_fwd_pipe_kernel(const Ti
             for (int t = 0; t < kLeanPasses; ++t) {
                 if (t < passes && ulv[t] < Qc) {
                     const bool livet = r0[t] >= 0;
-                    recs[ulv[t] * LPA + j1] = make_int4(livet ? (base + r0[t]) * scale : 0, livet ? (base + r1[t]) * scale : 0,
+                    recs[ulv[t] * LPA + (j1 ^ rec_swizzle(ulv[t]))] = make_int4(livet ? (base + r0[t]) * scale : 0, livet ? (base + r1[t]) * scale : 0,
                                                         __float_as_int(c0[t]), __float_as_int(c1[t]));
                     if (j1 == 0) uq[buf][ulv[t]] = qv[t];
                 }
@@ -208,13 +208,14 @@ __global__ void __launch_bounds__(kLeanThreads, 2) msda_fwd_pipe_kernel(const Ti
                 const int ul = ul0 + g;
                 const bool active = ul < gQc;
                 const int4 *rp = grecs + (active ? ul : 0) * LPA;
+                const int sw = rec_swizzle(active ? ul : 0);
                 float acc[NF];
 #pragma unroll
                 for (int k = 0; k < NF; ++k) acc[k] = 0.f;
                 for (int s = 0; s < LP4; s += 4) {
                     int4 r[4];
 #pragma unroll
-                    for (int b = 0; b < 4; ++b) r[b] = rp[s + b];
+                    for (int b = 0; b < 4; ++b) r[b] = rp[(s + b) ^ sw];
                     if (gstaged) {
 #pragma unroll
                         for (int b = 0; b < 4; ++b) {
