@@ -46,6 +46,16 @@ def load_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def load_traffic():
+    """DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of the headline kernels from the committed
+    `ncu --set full` capture (profiles/r1_traffic.json, written by tools/ncu_traffic.py); {} if absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
+
+
 def level_lengths(t0, n_levels=4):
     ts = [int(t0)]
     for _ in range(n_levels - 1):
@@ -431,13 +441,18 @@ def run_ours(args, world, rank, local):
     qps = queries_per_step * args.steps / (total_ms * 1e-3)
     elem = 2 if args.dtype == "bf16" else 4
     fb, bb = algorithmic_bytes(w, elem)
-    # dominant launch: the backward call (memset of the accumulation image + msda_bwd_fast_kernel)
-    roof = {"bound": "hbm", "kernel": "msda_fused_backward (cudaMemsetAsync(grad_value) + msda_bwd_fast_kernel)",
+    # dominant launch: the backward call = cudaMemsetAsync(grad_value) + msda_bwd_lean_kernel (csrc/msda_lean.cuh)
+    traffic = load_traffic()
+    roof = {"bound": "hbm", "kernel": "msda_fused_backward (cudaMemsetAsync(grad_value) + msda_bwd_lean_kernel)",
             "achieved": bb / (bwd_ms * 1e-3) / 1e9, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-            "frac": bb / (bwd_ms * 1e-3) / 1e9 / peak, "traffic": None,
+            "frac": bb / (bwd_ms * 1e-3) / 1e9 / peak, "traffic": traffic.get("backward_bytes_per_launch"),
+            "traffic_source": traffic.get("source"),
             "algorithmic_bytes_per_launch": bb, "ms_per_launch": bwd_ms,
-            "forward": {"kernel": "msda_fwd_fast_kernel", "achieved": fb / (fwd_ms * 1e-3) / 1e9,
-                        "frac": fb / (fwd_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_launch": fb, "ms_per_launch": fwd_ms},
+            "on_chip_note": "both kernels are bound by shared-memory wavefronts / issue slots, not HBM: the gather reads "
+                            "2*D*4 B of shared memory per sample (12.8x the HBM bytes); see DESIGN.md section 4",
+            "forward": {"kernel": "msda_fwd_lean_kernel", "achieved": fb / (fwd_ms * 1e-3) / 1e9,
+                        "frac": fb / (fwd_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_launch": fb, "ms_per_launch": fwd_ms,
+                        "traffic": traffic.get("forward_bytes_per_launch")},
             "fwd_bwd": {"achieved": (fb + bb) / ((fwd_ms + bwd_ms) * 1e-3) / 1e9,
                         "frac": (fb + bb) / ((fwd_ms + bwd_ms) * 1e-3) / 1e9 / peak}}
     e2e_steps = max(3, min(args.steps, 20))

@@ -318,6 +318,7 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
         // (profiles/r1_phases.txt); the TMA engine serialises small bulk copies
         constexpr int VPR = rb / 16;
         for (int l = 0; l < a.L; ++l) {
+            if (win_hi[l] < win_lo[l]) continue;   // level without a live sample (ZEROS padding can drop them all)
             const int nv = (win_hi[l] - win_lo[l] + 1) * VPR;
             for (int v = tid; v < nv; v += kLeanThreads) {
                 const int r = win_lo[l] + v / VPR, jj = v % VPR;

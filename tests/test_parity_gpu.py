@@ -329,3 +329,101 @@ def test_backward_run_to_run_variation_is_bounded(dvc):
     a = _np64(_run_core(dvc, t, inp["shapes"], "border")[1])
     b = _np64(_run_core(dvc, t, inp["shapes"], "border")[1])
     assert np.abs(a - b).max() <= 1e-5 * np.abs(a).max()
+
+
+# ------------------------------------------------------------------------------------------------
+# encoder self-attention geometry (Lq == S): level-grid tiling + staged value windows in both kernels
+# ------------------------------------------------------------------------------------------------
+def _encoder_inputs(seed, N, M, D, T0, P, jitter):
+    """Reference points on the level grids (deformable_transformer.py:198-208), offsets = the module's
+    initial bias (ms_deform_attn.py:62-71) + N(0, jitter) rows."""
+    import bench
+    rs = np.random.RandomState(seed)
+    T = cases.level_lengths(T0)
+    L, S = len(T), sum(T)
+    ref1 = np.concatenate([(np.arange(t) + 0.5) / t for t in T])
+    ref = np.broadcast_to(ref1[None, :, None, None], (N, S, L, 1)).copy()
+    bias = bench.offset_bias(M, L, P).numpy().astype(np.float64)
+    off = bias[None, None] + jitter * rs.standard_normal((N, S, M, L, P))
+    return dict(value=rs.standard_normal((N, S, M, D)), ref=ref, off=off,
+                logits=rs.standard_normal((N, S, M, L, P)), grad_out=rs.standard_normal((N, S, M * D)),
+                T=np.asarray(T, dtype=np.int64))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("pad", ["border", "zeros"])
+@pytest.mark.parametrize("cfg", [
+    dict(seed=31, N=2, M=8, D=64, T0=300, P=4, jitter=1.0),    # 10 time spans per (n, m): several tiles, halos
+    dict(seed=32, N=1, M=4, D=64, T0=521, P=4, jitter=6.0),    # odd lengths, wide windows
+    dict(seed=33, N=1, M=2, D=32, T0=160, P=8, jitter=40.0),   # windows that do not fit: L1 gather fallback
+])
+def test_encoder_geometry_vs_oracle(dvc, cfg, pad, dtype):
+    inp = _nudge_off_knots(_encoder_inputs(**cfg), cfg["P"])
+    dev = "cuda"
+    value = torch.from_numpy(inp["value"]).to(dtype).to(dev).requires_grad_(True)
+    ref = torch.from_numpy(inp["ref"]).float().to(dev).requires_grad_(True)
+    off = torch.from_numpy(inp["off"]).float().to(dev).requires_grad_(True)
+    logits = torch.from_numpy(inp["logits"]).float().to(dev).requires_grad_(True)
+    gout = torch.from_numpy(inp["grad_out"]).to(dtype).to(dev)
+    T = torch.from_numpy(inp["T"]).to(dev)
+    lsi = torch.from_numpy(cases.level_start_index(cases.as_shapes2(inp["T"]))).to(dev)
+    out = dvc.MSDeformAttnFusedFunction.apply(value, T, lsi, ref, off, logits, pad)
+    out.backward(gout)
+    torch.cuda.synchronize()
+    v64, r64, o64, l64, g64 = (_np64(x) for x in (value, ref, off, logits, gout))
+    want_out = O.fused_forward(v64, inp["T"], r64, o64, l64, PAD[pad])
+    gv, g_ref, g_off, g_logits = O.fused_backward(v64, inp["T"], r64, o64, l64, g64, PAD[pad])
+    _assert_close(_np64(out), want_out, dtype, "enc/out")
+    _assert_close(_np64(value.grad), gv, dtype, "enc/grad_value")
+    _assert_close(_np64(logits.grad), g_logits, dtype, "enc/grad_logits")
+    _assert_close(_np64(ref.grad), g_ref, dtype, "enc/grad_ref", rel_scale=4.0)
+    # grad_offsets is piecewise constant in the location: allow a 1e-3 fraction of knot-flip outliers
+    rel, ab = TOL[dtype]
+    d = np.abs(_np64(off.grad) - g_off)
+    assert (d > rel * np.abs(g_off).max() + ab).mean() < 1e-3
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_full_size_properties(dvc, dtype):
+    """BASELINE.json-sized problem (bench.py's headline workload) where the oracle is too slow: size-independent
+    properties.  (1) out is linear in value, so <out, g> == <value, grad_value> (adjointness);
+    (2) softmax Jacobian: sum over (l, p) of grad_logits is 0 for every (n, q, m);
+    (3) the fused entry points agree with the unfused ones fed torch-computed locations / weights;
+    (4) the first video of the batch agrees with the fp64 oracle on a slice of its queries."""
+    import bench
+    cfg = dict(bench.HEADLINE)
+    w = bench.make_workload(cfg["N"], cfg["T0"], cfg["M"], cfg["D"], cfg["L"], cfg["P"], cfg["kind"], "cuda", dtype=dtype, seed=7)
+    value = w["value"].clone().requires_grad_(True)
+    off = w["off"].clone().requires_grad_(True)
+    logits = w["logits"].clone().requires_grad_(True)
+    out = dvc.MSDeformAttnFusedFunction.apply(value, w["shapes"], w["lsi"], w["ref"], off, logits, "border")
+    out.backward(w["grad_out"])
+    torch.cuda.synchronize()
+    assert torch.isfinite(out).all() and torch.isfinite(value.grad).all()
+    lhs = float((out.detach().double() * w["grad_out"].double()).sum())
+    rhs = float((value.detach().double() * value.grad.double()).sum())
+    scale = float((out.detach().double().abs() * w["grad_out"].double().abs()).sum())
+    assert abs(lhs - rhs) <= (3e-3 if dtype == torch.bfloat16 else 1e-5) * scale, (lhs, rhs, scale)
+    gl = logits.grad.double().flatten(-2).sum(-1)
+    assert float(gl.abs().max()) <= 1e-4 * float(logits.grad.abs().max()) * (50 if dtype == torch.bfloat16 else 1) + 1e-6
+    # (3) unfused path on torch-computed loc / attn (a 4-video slice keeps the temporaries small)
+    nb = 4
+    Tt = w["shapes"].float()
+    attn = torch.softmax(w["logits"][:nb].flatten(-2), -1).view_as(w["logits"][:nb]).contiguous()
+    x = w["ref"][:nb, :, None, :, None, 0] + w["off"][:nb] / Tt[None, None, None, :, None]
+    loc = torch.stack((x, torch.full_like(x, 0.5)), -1).contiguous()
+    shapes2 = torch.stack([torch.ones_like(w["shapes"]), w["shapes"]], -1).contiguous()
+    v2 = w["value"][:nb].clone().requires_grad_(True)
+    out2 = dvc.MSDeformAttnFunction.apply(v2, shapes2, w["lsi"], loc, attn, 64, "border", True)
+    out2.backward(w["grad_out"][:nb].contiguous())
+    rel = 2e-2 if dtype == torch.bfloat16 else 3e-4   # x recomputed in fp32 outside the kernel: a few knot flips
+    d = (out2.detach().double() - out[:nb].detach().double()).abs()
+    assert float((d > rel * float(out.detach().abs().max())).double().mean()) < 1e-3
+    dgv = (v2.grad.double() - value.grad[:nb].double()).abs()
+    assert float((dgv > rel * float(value.grad.abs().max())).double().mean()) < 1e-3
+    # (4) oracle on a query slice of video 0 (queries only matter through their own rows of the inputs)
+    q0, q1 = 900, 1100
+    T = np.asarray(w["T"], dtype=np.int64)
+    v64 = _np64(w["value"][:1])
+    want = O.fused_forward(v64, T, _np64(w["ref"][:1, q0:q1]), _np64(w["off"][:1, q0:q1]), _np64(w["logits"][:1, q0:q1]), O.BORDER)
+    _assert_close(_np64(out[:1, q0:q1]), want, dtype, "full/out-slice")
