@@ -26,7 +26,7 @@ for _ in range(reps):
     op.backward()
 e.record(); torch.cuda.synchronize(); tb = s.elapsed_time(e) / reps
 lib.msda_dev_phase_clocks(buf, 1)
-names = [["loop top", "A decode", "sync1 wait", "B stage+recs", "C next raw issue", "cp.async wait", "sync2 wait", "D gather"] if os.environ.get("MSDA_PIPE", "1") != "0" else ["init", "raw+decode", "window calc", "bulk issue+recs", "mbar wait", "gather+store"],
+names = [["init", "raw+decode", "window calc", "bulk issue+recs", "mbar wait", "gather+store"],
          ["init", "raw+decode", "G cp.async+zero", "histogram", "scan a", "scan b", "scatter+cp wait", "row sweep", "sample grads"]]
 for k, (nm, t) in enumerate(zip(names, (tf, tb))):
     v = [buf[k * 16 + i] for i in range(16)]
