@@ -12,7 +12,6 @@
 #include "msda_generic.cuh"
 #include "msda_tile.cuh"
 #include "msda_lean.cuh"
-#include "msda_pipe.cuh"
 
 using namespace msda;
 
@@ -329,30 +328,12 @@ int launch_lean_inst(const TileArgs &a, const LeanPlan &p, cudaStream_t st)
     return check_launch();
 }
 
-// persistent pipelined forward (msda_pipe.cuh): 2 CTAs per SM, double-buffered records + window
-template <typename VT, int LPG, int NCH, int LPA, bool FUSED>
-int launch_pipe_inst(const TileArgs &a, const LeanPlan &p, cudaStream_t st)
-{
-    static unsigned long long done = 0;
-    if (int e = allow_big_smem(msda_fwd_pipe_kernel<VT, LPG, NCH, LPA, FUSED>, done)) return e;
-    const long long tiles = (long long)p.chunks * a.M * a.N;
-    const int grid = (int)(tiles < 2 * kNumSMs ? tiles : 2 * kNumSMs);
-    msda_fwd_pipe_kernel<VT, LPG, NCH, LPA, FUSED><<<grid, kLeanThreads, 2 * p.smem, st>>>(a);
-    return check_launch();
-}
-
 template <typename VT, bool FUSED, bool BWD> int launch_lean_shape(const TileArgs &a, const LeanPlan &p, cudaStream_t st)
 {
-    static const int use_pipe = env_int("MSDA_PIPE", 0);
-    const bool pipe = !BWD && use_pipe && 2 * p.smem <= 110 * 1024 && (long long)p.chunks * a.M * a.N < (1ll << 31);
 #define MSDA_LEAN_CASE(LPG_, NCH_)                                                                       \
-    if (p.lpg == LPG_ && p.nch == NCH_) {                                                                \
-        if (pipe)                                                                                        \
-            return p.lpa == 16 ? launch_pipe_inst<VT, LPG_, NCH_, 16, FUSED>(a, p, st)                   \
-                               : launch_pipe_inst<VT, LPG_, NCH_, 32, FUSED>(a, p, st);                  \
+    if (p.lpg == LPG_ && p.nch == NCH_)                                                                  \
         return p.lpa == 16 ? launch_lean_inst<VT, LPG_, NCH_, 16, FUSED, BWD>(a, p, st)                  \
-                           : launch_lean_inst<VT, LPG_, NCH_, 32, FUSED, BWD>(a, p, st);                 \
-    }
+                           : launch_lean_inst<VT, LPG_, NCH_, 32, FUSED, BWD>(a, p, st);
 #ifndef MSDA_DEV_FAST   // development builds instantiate the headline shape only
     MSDA_LEAN_CASE(4, 1)
     MSDA_LEAN_CASE(8, 1)
