@@ -417,6 +417,60 @@ def small_shape_latency(device):
     return res
 
 
+def reference_cuda_same_box(w, steps=20):
+    """The reference's own CUDA kernels (pdvc/ops/src, compiled unmodified for sm_100 by tools/build_ref_cuda.py into
+    baseline/_ref/ref_cuda/) on the same workload and box: unfused boundary (locations and softmaxed weights
+    precomputed, as ms_deform_attn.py:100-122 hands them over), ZEROS padding, its own allocations and memsets
+    (ms_deform_attn_cuda.cu:54, :121-123).  Our unfused entry points are timed beside it on the same tensors."""
+    import importlib.util
+    so = os.path.join(ROOT, "baseline", "_ref", "ref_cuda", "MultiScaleDeformableAttention_refcuda.so")
+    if not os.path.exists(so):
+        return {"unavailable": "baseline/_ref/ref_cuda not built (tools/build_ref_cuda.py needs /root/reference)"}
+    spec = importlib.util.spec_from_file_location("MultiScaleDeformableAttention_refcuda", so)
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    import dense_video_captioning_b200 as dvc
+    N, Lq, M, D, L, P = (w[k] for k in ("N", "Lq", "M", "D", "L", "P"))
+    Tt = w["shapes"].float()
+    attn = torch.softmax(w["logits"].flatten(-2), -1).view_as(w["logits"]).contiguous()
+    x = w["ref"][:, :, None, :, None, 0] + w["off"] / Tt[None, None, None, :, None]
+    loc = torch.stack((x, torch.full_like(x, 0.5)), -1).contiguous()
+    shapes2 = torch.stack((torch.ones_like(w["shapes"]), w["shapes"]), -1).contiguous()
+    value, gout = w["value"].float().contiguous(), w["grad_out"].float().contiguous()
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(steps):
+            fn()
+        e.record()
+        torch.cuda.synchronize()
+        return s.elapsed_time(e) / steps
+
+    r_fwd = timed(lambda: ref.ms_deform_attn_forward(value, shapes2, w["lsi"], loc, attn, 64))
+    r_bwd = timed(lambda: ref.ms_deform_attn_backward(value, shapes2, w["lsi"], loc, attn, gout, 64))
+    from dense_video_captioning_b200.ops.functions import ms_deform_attn_func as fn_mod
+    compat_dir = os.path.join(os.path.dirname(os.path.abspath(dvc.__file__)), "compat")
+    if compat_dir not in sys.path:
+        sys.path.insert(0, compat_dir)
+    import MultiScaleDeformableAttention as ours   # the drop-in for the reference's extension module
+    prev = fn_mod.get_default_padding_mode()
+    fn_mod.set_default_padding_mode("zeros")
+    try:
+        o_fwd = timed(lambda: ours.ms_deform_attn_forward(value, shapes2, w["lsi"], loc, attn, 64))
+        o_bwd = timed(lambda: ours.ms_deform_attn_backward(value, shapes2, w["lsi"], loc, attn, gout, 64))
+    finally:
+        fn_mod.set_default_padding_mode(prev)
+    q = N * Lq
+    return {"boundary": "unfused (sampling_locations + attention_weights in), ZEROS padding, fp32",
+            "reference_cuda": {"fwd_ms": r_fwd, "bwd_ms": r_bwd, "queries_per_s": q / ((r_fwd + r_bwd) * 1e-3)},
+            "ours_unfused": {"fwd_ms": o_fwd, "bwd_ms": o_bwd, "queries_per_s": q / ((o_fwd + o_bwd) * 1e-3)},
+            "speedup_fwd_bwd": (r_fwd + r_bwd) / (o_fwd + o_bwd)}
+
+
 def run_ours(args, world, rank, local):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py (our arm) needs a CUDA device: there is no CPU fallback for the MSDA kernels")
@@ -489,6 +543,10 @@ def run_ours(args, world, rank, local):
                                               f"{reps} reps in {dt:.1f} s; oracle/core_pytorch.py fwd+bwd"}
         if world == 1 and not args.no_extra:
             line["extra"] = {"small_shapes": small_shape_latency(device)}
+            try:
+                line["extra"]["reference_cuda_same_box"] = reference_cuda_same_box(w)
+            except Exception as ex:   # the comparison must never cost the bench line
+                line["extra"]["reference_cuda_same_box"] = {"error": repr(ex)}
         print(json.dumps(line), flush=True)
 
 

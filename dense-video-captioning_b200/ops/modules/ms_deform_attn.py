@@ -80,7 +80,17 @@ class _MSDeformFrontEnd(nn.Module):
         xavier_uniform_(self.output_proj.weight.data)
         constant_(self.output_proj.bias.data, 0.)
 
-    def _project(self, query, reference_points, input_flatten, input_spatial_shapes, input_padding_mask):
+    def project_value(self, input_flatten, input_padding_mask=None):
+        """value_proj + padding mask (ms_deform_attn.py:95-98) -> (N,S,M,D).  Callers that attend to the same memory
+        many times (the caption LSTM, one call per word) may compute it once and pass it as `projected_value`."""
+        N, Len_in, _ = input_flatten.shape
+        value = self.value_proj(input_flatten)
+        if input_padding_mask is not None:
+            value = value.masked_fill(input_padding_mask[..., None], float(0))
+        return value.view(N, Len_in, self.n_heads, self.d_model // self.n_heads)
+
+    def _project(self, query, reference_points, input_flatten, input_spatial_shapes, input_padding_mask,
+                 projected_value=None):
         """value (N,S,M,D), raw offsets and logits (N,Lq,M,L,P) -- ms_deform_attn.py:95-100."""
         if not query.is_cuda:
             raise RuntimeError("MSDeformAttn (B200 build) runs on CUDA tensors only: there is no CPU path "
@@ -91,10 +101,7 @@ class _MSDeformFrontEnd(nn.Module):
         if reference_points.shape[-1] not in (1, 2):
             raise ValueError('Last dim of reference_points must be 1 or 2, but get {} instead.'.format(
                 reference_points.shape[-1]))
-        value = self.value_proj(input_flatten)
-        if input_padding_mask is not None:
-            value = value.masked_fill(input_padding_mask[..., None], float(0))
-        value = value.view(N, Len_in, self.n_heads, self.d_model // self.n_heads)
+        value = projected_value if projected_value is not None else self.project_value(input_flatten, input_padding_mask)
         offsets = self.sampling_offsets(query).view(N, Len_q, self.n_heads, self.n_levels, self.n_points)
         logits = self.attention_weights(query).view(N, Len_q, self.n_heads, self.n_levels, self.n_points)
         return value, offsets, logits

@@ -16,9 +16,9 @@ class MSDeformAttnCap(_MSDeformFrontEnd):
         super().__init__(d_model, n_levels, n_heads, n_points)
 
     def forward(self, query, reference_points, input_flatten, input_spatial_shapes, input_level_start_index,
-                input_padding_mask=None):
+                input_padding_mask=None, projected_value=None):
         value, offsets, logits = self._project(query, reference_points, input_flatten, input_spatial_shapes,
-                                               input_padding_mask)
+                                               input_padding_mask, projected_value)
         # the attention weights are computed by the reference too (:102-103) but do not reach the output
         loc, _, shapes2 = self._locations_and_weights(reference_points, offsets, logits, input_spatial_shapes)
         value = value.contiguous()

@@ -1,0 +1,138 @@
+"""Synthetic-feature PDVC training harness (BASELINE.json metric 2: training videos/s at 1/2/4/8 GPUs).
+
+What the reference does per iteration (train.py:163-194): move the batch to the device, forward with the criterion,
+weighted loss sum, backward, clip_grad_norm_(100), Adam step -- batch size 1 video, with a `cuda.synchronize()` before
+and after every iteration.  Same step here, minus the two forced synchronisations, with the inputs copied from pinned
+host memory each step, and -- new, the reference never wraps PDVC in DDP (SURVEY finding 0.8) -- one process per GPU with
+`DistributedDataParallel` (NCCL all-reduce of the gradients, bucketed and overlapped with backward).  Ranks own
+disjoint videos (video i of step s goes to rank i); the learning rate is not rescaled (the reference has no rule).
+
+Configurations: shapes from cfgs/anet_c3d_pdvc.yml (+ cfgs/anet_c3d_pdvcl.yml), cfgs/yc2_tsp_pdvc.yml as
+shipped and with the YouCook2 overrides of cfgs/yc2_tsn_pdvcl.yml:26,31, and the PDVC core of
+cfgs/yc2_newModel_sound.yml on synthetic 768-d features.
+"""
+import contextlib
+from dataclasses import replace
+
+import numpy as np
+import torch
+
+from .model import PDVCConfig, build
+
+CONFIGS = {
+    # BASELINE configs[2]: ActivityNet C3D, 100 frame embeddings, 10 queries
+    "anet_c3d_pdvc": dict(cfg=PDVCConfig(feature_dim=500, num_queries=10, frame_embedding_num=100, vocab_size=5747,
+                                         max_eseq_length=10), n_gt=4, cap_len=12, amp=False),
+    # BASELINE configs[1] as shipped: inherits the ActivityNet shapes, only the feature type/dim change
+    "yc2_tsp_pdvc": dict(cfg=PDVCConfig(feature_dim=512, num_queries=10, frame_embedding_num=100, vocab_size=5747,
+                                        max_eseq_length=10), n_gt=6, cap_len=12, amp=False),
+    # BASELINE configs[1] with the YouCook2 shapes of configs[0] (100 queries, 200 frames, vocab 1607)
+    "yc2_tsp_pdvc_yc2shape": dict(cfg=PDVCConfig(feature_dim=512, num_queries=100, frame_embedding_num=200,
+                                                 vocab_size=1607, max_eseq_length=20), n_gt=6, cap_len=12, amp=False),
+    # BASELINE configs[3]: PDVC core of yc2_newModel_sound (3+3 layers, 768-d fused features), bf16 autocast
+    "yc2_newmodel_core_bf16": dict(cfg=PDVCConfig(feature_dim=768, num_queries=100, frame_embedding_num=200,
+                                                  vocab_size=1607, max_eseq_length=20, enc_layers=3, dec_layers=3),
+                                   n_gt=6, cap_len=12, amp=True),
+}
+
+
+def synthetic_video(cfg, n_gt, cap_len, seed):
+    """One video's batch dict on the HOST (pinned where a GPU exists), SURVEY 8d config-2 inputs: features ~ N(0,1),
+    all frames valid, duration 120 s, n_gt events with centre U(0.2,0.8) and length U(0.05,0.25), label 0, captions of
+    cap_len random tokens framed by 0 (BOS/EOS) and padded to cap_len + 4."""
+    rs = np.random.RandomState(seed)
+    T = cfg.frame_embedding_num
+    words = cap_len + 4
+    feats = rs.standard_normal((1, T, cfg.feature_dim)).astype(np.float32)
+    centre = rs.uniform(0.2, 0.8, n_gt)
+    length = rs.uniform(0.05, 0.25, n_gt)
+    boxes = np.stack([centre, length], -1).astype(np.float32)
+    caps = np.zeros((n_gt, words), dtype=np.int64)
+    caps[:, 1:1 + cap_len] = rs.randint(1, cfg.vocab_size, (n_gt, cap_len))
+    cap_mask = np.zeros((n_gt, words), dtype=np.float32)
+    cap_mask[:, :cap_len + 2] = 1.0
+    host = {
+        'video_tensor': torch.from_numpy(feats),
+        'video_mask': torch.ones(1, T, dtype=torch.bool),
+        'video_length': torch.tensor([[float(T), 120.0, float(n_gt)]]),
+        'boxes': torch.from_numpy(boxes),
+        'labels': torch.zeros(n_gt, dtype=torch.long),
+        'cap_tensor': torch.from_numpy(caps),
+        'cap_mask': torch.from_numpy(cap_mask),
+    }
+    if torch.cuda.is_available():
+        host = {k: v.pin_memory() for k, v in host.items()}
+    return host
+
+
+def to_device(host, device):
+    """The host->device boundary of the step (train.py:174-177)."""
+    d = {k: v.to(device, non_blocking=True) for k, v in host.items()}
+    return {'video_tensor': d['video_tensor'], 'video_mask': d['video_mask'], 'video_length': d['video_length'],
+            'video_target': [{'boxes': d['boxes'], 'labels': d['labels']}],
+            'cap_tensor': d['cap_tensor'], 'cap_mask': d['cap_mask'], 'cap_tensor_host': host['cap_tensor'].numpy()}
+
+
+def input_bytes(host):
+    return sum(v.numel() * v.element_size() for v in host.values())
+
+
+class Trainer:
+    """model + criterion + Adam(lr 5e-5, wd 1e-4) + grad clip 100 (cfgs/anet_c3d_pdvcl.yml:17,21; opts.py:104-105)."""
+
+    def __init__(self, name_or_cfg, device, world_size=1, lr=5e-5, weight_decay=1e-4, grad_clip=100.0, amp=None,
+                 seed=0, dropout=None):
+        spec = CONFIGS[name_or_cfg] if isinstance(name_or_cfg, str) else dict(cfg=name_or_cfg, n_gt=4, cap_len=12, amp=False)
+        cfg = spec["cfg"]
+        if dropout is not None:
+            cfg = replace(cfg, transformer_dropout_prob=dropout, drop_prob=dropout)
+        self.cfg, self.n_gt, self.cap_len = cfg, spec["n_gt"], spec["cap_len"]
+        self.amp = spec["amp"] if amp is None else amp
+        self.device = torch.device(device)
+        torch.manual_seed(seed)                      # identical initial weights on every rank
+        self.model, self.criterion = build(cfg)
+        self.model.to(self.device).train()
+        self.criterion.to(self.device)
+        # parameters the learnt-query path never touches (proposal embedding, deformable_transformer.py:136-142): without
+        # a gradient Adam skips them in the reference as well; freezing them keeps DDP's graph static
+        for name, p in self.model.named_parameters():
+            if name.startswith(("transformer.pos_trans.", "transformer.pos_trans_norm.")):
+                p.requires_grad_(False)
+        self.params = [p for p in self.model.parameters() if p.requires_grad]
+        self.net = self.model
+        if world_size > 1:
+            from torch.nn.parallel import DistributedDataParallel as DDP
+            ids = [self.device.index] if self.device.type == "cuda" else None
+            self.net = DDP(_StepModule(self.model, self.criterion), device_ids=ids, gradient_as_bucket_view=True,
+                           broadcast_buffers=False)
+        else:
+            self.net = _StepModule(self.model, self.criterion)
+        self.optimizer = torch.optim.Adam(self.params, lr=lr, weight_decay=weight_decay)
+        self.grad_clip = grad_clip
+        self.weight_dict = self.criterion.weight_dict
+
+    def step(self, host_batch):
+        """One training iteration on one video; returns the (device) total loss without synchronising."""
+        dt = to_device(host_batch, self.device)
+        self.optimizer.zero_grad(set_to_none=True)
+        ctx = torch.autocast(self.device.type, dtype=torch.bfloat16) if self.amp else contextlib.nullcontext()
+        with ctx:
+            losses = self.net(dt)
+        total = sum(losses[k].float() * w for k, w in self.weight_dict.items() if k in losses)
+        total.backward()
+        torch.nn.utils.clip_grad_norm_(self.params, self.grad_clip)
+        self.optimizer.step()
+        self.last_losses = losses
+        return total.detach()
+
+
+class _StepModule(torch.nn.Module):
+    """forward(dt) -> loss dict; the unit DDP wraps (criterion included: it has no parameters)."""
+
+    def __init__(self, model, criterion):
+        super().__init__()
+        self.model = model
+        self.criterion = criterion
+
+    def forward(self, dt):
+        return self.model(dt, self.criterion)[1]

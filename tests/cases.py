@@ -145,3 +145,60 @@ def checksum(d):
         a = np.asarray(d[k], dtype=np.float64).ravel()
         acc += float(np.dot(a, np.cos(np.arange(a.size) * 0.37 + 1.0)))
     return acc
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# whole-model (PDVC) fixtures: parameters are filled from a per-name seeded formula instead of being stored, so the
+# reference model (tests/golden/make_golden_pdvc.py, build container) and this package's model (tests) hold identical
+# weights without an 80 MB fixture.
+# ---------------------------------------------------------------------------------------------------------------
+def canonical_param_name(key):
+    """Aliases of one shared tensor map to one name: the decoder's refinement heads are the model's bbox heads
+    (pdvc/pdvc.py:93-99) and, with share_caption_head, every caption_head.<i> is caption_head.0 (pdvc.py:80-82)."""
+    import re
+    key = key.replace("transformer.decoder.bbox_head.", "bbox_head.")
+    return re.sub(r"^caption_head\.\d+\.", "caption_head.0.", key)
+
+
+def fill_parameters(model, share_caption_head=True):
+    """Overwrite every parameter/buffer of `model` (reference PDVC or ours: same state_dict keys) in place."""
+    import re
+    import zlib
+    import torch
+    with torch.no_grad():
+        for key, t in model.state_dict().items():
+            if not t.dtype.is_floating_point:
+                continue
+            name = canonical_param_name(key) if share_caption_head else key.replace("transformer.decoder.bbox_head.", "bbox_head.")
+            rs = np.random.RandomState(zlib.crc32(name.encode()) & 0x7FFFFFFF)
+            z = rs.standard_normal(tuple(t.shape))
+            if t.dim() >= 2:
+                new = z * (0.5 / np.sqrt(float(np.prod(t.shape[1:]))))
+            elif re.search(r"(norm\d*\.weight|input_proj\.\d+\.1\.weight)$", name):
+                new = 1.0 + 0.05 * z
+            elif name.endswith("sampling_offsets.bias"):
+                new = t.detach().double().cpu().numpy() + 0.1 * z
+            else:
+                new = 0.05 * z
+            t.copy_(torch.from_numpy(np.ascontiguousarray(new)).to(t.dtype))
+
+
+def pdvc_batch(seed, T, feature_dim, n_gt, cap_len, vocab_size, dtype="float64"):
+    """Synthetic single-video batch as numpy arrays."""
+    rs = np.random.RandomState(seed)
+    words = cap_len + 4
+    centre, length = rs.uniform(0.2, 0.8, n_gt), rs.uniform(0.05, 0.25, n_gt)
+    caps = np.zeros((n_gt, words), dtype=np.int64)
+    caps[:, 1:1 + cap_len] = rs.randint(1, vocab_size, (n_gt, cap_len))
+    # ragged sentence lengths: some captions end early
+    for g in range(n_gt):
+        caps[g, 1 + cap_len - (g % 3):] = 0
+    mask = np.zeros((n_gt, words))
+    for g in range(n_gt):
+        mask[g, :cap_len - (g % 3) + 2] = 1.0
+    valid = np.ones((1, T), dtype=bool)
+    valid[0, T - T // 8:] = False            # padded tail: exercises the padding mask and valid ratios
+    return dict(video_tensor=rs.standard_normal((1, T, feature_dim)).astype(dtype), video_mask=valid,
+                video_length=np.array([[float(T), 117.6, float(n_gt)]], dtype=dtype),
+                boxes=np.stack([centre, length], -1).astype(dtype), labels=np.zeros(n_gt, dtype=np.int64),
+                cap_tensor=caps, cap_mask=mask.astype(dtype))

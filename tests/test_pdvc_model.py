@@ -1,0 +1,143 @@
+"""Whole-model parity of the PDVC harness (dense-video-captioning_b200/pdvc) against the UNMODIFIED reference model.
+
+tests/golden/pdvc_anet_c3d.npz holds every loss term, the matched indices, the head outputs and the gradient norm +
+checksum of every parameter of the reference's PDVC (cfgs/anet_c3d_pdvc.yml, dropout 0, float64) on a seeded synthetic
+video; weights on both sides come from cases.fill_parameters().
+
+  * CPU (not gpu): the host logic of this package's model -- everything except the two CUDA modules, which are replaced
+    IN THE TEST by the oracle's torch restatement (oracle/core_pytorch.module_forward) -- reproduces the reference to
+    float64 round-off.  This checks transformer / heads / matcher / criterion / captioner, not the kernels.
+  * GPU: the real thing, fp32, CUDA kernels through the C ABI, against the same golden numbers.
+"""
+import numpy as np
+import pytest
+import torch
+
+import cases
+from conftest import load_golden
+from oracle import core_pytorch
+
+
+def _cfg(golden):
+    from dense_video_captioning_b200.pdvc import PDVCConfig
+    return PDVCConfig(feature_dim=500, num_queries=10, frame_embedding_num=100, vocab_size=int(golden["vocab_size"]),
+                      max_eseq_length=10, transformer_dropout_prob=0.0, drop_prob=0.0)
+
+
+def _batch(cfg, dtype, device):
+    b = cases.pdvc_batch(5, cfg.frame_embedding_num, cfg.feature_dim, n_gt=4, cap_len=9, vocab_size=cfg.vocab_size)
+    t = {k: torch.from_numpy(v) for k, v in b.items()}
+    f = lambda x: x.to(dtype).to(device)  # noqa: E731
+    return {"video_tensor": f(t["video_tensor"]), "video_mask": t["video_mask"].to(device),
+            "video_length": f(t["video_length"]),
+            "video_target": [{"boxes": f(t["boxes"]), "labels": t["labels"].to(device)}],
+            "cap_tensor": t["cap_tensor"].to(device), "cap_mask": f(t["cap_mask"]), "cap_tensor_host": b["cap_tensor"]}
+
+
+def _run(model, criterion, dt):
+    out, loss = model(dt, criterion)
+    wd = criterion.weight_dict
+    total = sum(loss[k] * wd[k] for k in loss if k in wd)
+    total.backward()
+    return out, loss, total
+
+
+def _check(golden, model, out, loss, total, rel_loss, rel_grad):
+    want = dict(zip([str(n) for n in golden["loss_names"]], golden["loss_values"]))
+    assert set(want) == set(loss), (sorted(want), sorted(loss))
+    for k, v in want.items():
+        assert abs(float(loss[k]) - v) <= rel_loss * max(abs(v), 1.0), f"{k}: {float(loss[k])} vs {v}"
+    assert abs(float(total) - float(golden["total_loss"])) <= rel_loss * float(golden["total_loss"])
+    q, t = out["matched_indices"][0]
+    assert q.tolist() == golden["matched_query"].tolist() and t.tolist() == golden["matched_target"].tolist()
+    for key in ("pred_boxes", "pred_logits", "pred_count"):
+        got = out[key].detach().double().cpu().numpy()
+        assert np.abs(got - golden[key]).max() <= rel_loss * max(1.0, np.abs(golden[key]).max()), key
+    grads = {}
+    for key, p in model.named_parameters():
+        name = cases.canonical_param_name(key)
+        if p.grad is not None and name not in grads:
+            g = p.grad.detach().double().cpu()
+            w = torch.arange(1, g.numel() + 1, dtype=torch.float64).view_as(g).remainder(7).add(1)
+            grads[name] = (float(g.norm()), float((g * w).sum()))
+    names = [str(n) for n in golden["grad_names"]]
+    assert set(names) == set(grads), set(names) ^ set(grads)
+    for n, norm, chk in zip(names, golden["grad_norms"], golden["grad_checksums"]):
+        assert abs(grads[n][0] - norm) <= rel_grad * max(norm, 1e-3), f"|grad {n}|: {grads[n][0]} vs {norm}"
+        assert abs(grads[n][1] - chk) <= rel_grad * 50 * max(norm, 1e-3), f"checksum grad {n}: {grads[n][1]} vs {chk}"
+
+
+@pytest.fixture
+def oracle_modules(monkeypatch):
+    """Replace the two CUDA modules' forward by the CPU oracle -- test infrastructure, CPU leg only."""
+    from dense_video_captioning_b200.ops.modules import MSDeformAttn, MSDeformAttnCap
+
+    def attn_forward(self, query, reference_points, input_flatten, shapes, starts, padding_mask=None):
+        return core_pytorch.module_forward(dict(self.named_parameters()), query, reference_points, input_flatten, shapes,
+                                           padding_mask, self.n_heads, self.n_levels, self.n_points)
+
+    def cap_forward(self, query, reference_points, input_flatten, shapes, starts, padding_mask=None, projected_value=None):
+        return core_pytorch.module_forward(dict(self.named_parameters()), query, reference_points, input_flatten, shapes,
+                                           padding_mask, self.n_heads, self.n_levels, self.n_points, caption=True)
+
+    monkeypatch.setattr(MSDeformAttn, "forward", attn_forward)
+    monkeypatch.setattr(MSDeformAttnCap, "forward", cap_forward)
+
+
+def test_host_logic_matches_reference_model_float64(oracle_modules):
+    from dense_video_captioning_b200.pdvc import build
+    golden = load_golden("pdvc_anet_c3d")
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(torch.float64)
+    try:
+        cfg = _cfg(golden)
+        model, criterion = build(cfg)
+        model.double().train()
+        cases.fill_parameters(model)
+        out, loss, total = _run(model, criterion, _batch(cfg, torch.float64, "cpu"))
+        _check(golden, model, out, loss, total, rel_loss=1e-9, rel_grad=1e-7)
+    finally:
+        torch.set_default_dtype(prev)
+
+
+def test_state_dict_keys_follow_the_reference():
+    from dense_video_captioning_b200.pdvc import PDVCConfig, build
+    model, _ = build(PDVCConfig(vocab_size=50))
+    keys = set(model.state_dict().keys())
+    for k in ("base_encoder.input_proj.3.0.weight", "base_encoder.pos_embed.duration_embed_layer.bias",
+              "transformer.level_embed", "transformer.encoder.layers.1.self_attn.sampling_offsets.bias",
+              "transformer.decoder.layers.0.cross_attn.value_proj.weight", "transformer.decoder.layers.0.self_attn.in_proj_weight",
+              "transformer.decoder.bbox_head.1.layers.2.bias", "transformer.reference_points.weight", "transformer.pos_trans_norm.weight",
+              "query_embed.weight", "class_head.1.bias", "count_head.0.weight", "bbox_head.0.layers.0.weight",
+              "caption_head.0.embed.weight", "caption_head.1.logit.bias", "caption_head.0.core.rnn.weight_ih_l0",
+              "caption_head.0.core.deformable_att.sampling_offsets.weight", "caption_head.0.core.ctx2att.weight",
+              "caption_head.0.core.h2att.bias", "caption_head.0.core.alpha_net.weight"):
+        assert k in keys, k
+    golden = load_golden("pdvc_anet_c3d")
+    have = {cases.canonical_param_name(k) for k, p in model.named_parameters()}
+    assert {str(n) for n in golden["grad_names"]} <= have
+
+
+@pytest.mark.gpu
+def test_cuda_model_matches_reference_model_fp32():
+    from dense_video_captioning_b200.pdvc import build
+    golden = load_golden("pdvc_anet_c3d")
+    cfg = _cfg(golden)
+    model, criterion = build(cfg)
+    model.cuda().train()
+    criterion.cuda()
+    cases.fill_parameters(model)
+    out, loss, total = _run(model, criterion, _batch(cfg, torch.float32, "cuda"))
+    torch.cuda.synchronize()
+    # fp32 model vs float64 reference: losses to 2e-4 relative, parameter-gradient norms to 2e-3
+    _check(golden, model, out, loss, total, rel_loss=2e-4, rel_grad=2e-3)
+
+
+@pytest.mark.gpu
+def test_trainer_steps_and_loss_decreases():
+    from dense_video_captioning_b200.pdvc import Trainer, synthetic_video
+    tr = Trainer("anet_c3d_pdvc", "cuda:0", dropout=0.0, lr=1e-4)
+    video = synthetic_video(tr.cfg, tr.n_gt, tr.cap_len, seed=1)
+    losses = [float(tr.step(video)) for _ in range(12)]
+    assert all(np.isfinite(losses)), losses
+    assert losses[-1] < losses[0], losses
