@@ -471,6 +471,82 @@ def reference_cuda_same_box(w, steps=20):
             "speedup_fwd_bwd": (r_fwd + r_bwd) / (o_fwd + o_bwd)}
 
 
+def pdvc_train_leg(args, world, rank, device):
+    """BASELINE metric 2: PDVC training videos/s (one video per rank per step, DDP gradient all-reduce over NCCL when
+    world > 1).  Every step copies its video from pinned host memory and reads the loss back (e2e by construction)."""
+    from dense_video_captioning_b200.pdvc import CONFIGS, Trainer, synthetic_video
+    from dense_video_captioning_b200.pdvc.train import input_bytes
+    names = args.pdvc_configs.split(",") if args.pdvc_configs else list(CONFIGS)
+    res = {}
+    for name in names:
+        tr = Trainer(name, device, world_size=world)
+        videos = [synthetic_video(tr.cfg, tr.n_gt, tr.cap_len, seed=7919 * i + rank) for i in range(8)]
+        for i in range(args.pdvc_warmup):
+            tr.step(videos[i % len(videos)])
+        torch.cuda.synchronize()
+        barrier(world)
+        torch.cuda.synchronize()
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        start.record()
+        last = None
+        for i in range(args.pdvc_steps):
+            last = float(tr.step(videos[i % len(videos)]))      # device->host read of the step's loss
+        end.record()
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        barrier(world)
+        ms = max_over_ranks(start.elapsed_time(end), world, device)
+        n_params = sum(p.numel() for p in tr.params)
+        res[name] = {"videos_per_s": world * args.pdvc_steps / (ms * 1e-3), "ms_per_step": ms / args.pdvc_steps,
+                     "steps": args.pdvc_steps, "warmup": args.pdvc_warmup, "videos_per_step": world,
+                     "wall_s_rank0": wall, "final_loss": last, "trainable_params": n_params,
+                     "allreduce_bytes_per_step": 4 * n_params if world > 1 else 0,
+                     "h2d_bytes_per_step": input_bytes(videos[0]), "d2h_bytes_per_step": 4,
+                     "dtype": "bf16 autocast (MSDA kernels bf16 value, fp32 index side)" if tr.amp else "f32",
+                     "shape": {"T": tr.cfg.frame_embedding_num, "queries": tr.cfg.num_queries,
+                               "enc_layers": tr.cfg.enc_layers, "dec_layers": tr.cfg.dec_layers,
+                               "feature_dim": tr.cfg.feature_dim, "vocab": tr.cfg.vocab_size, "n_gt": tr.n_gt,
+                               "caption_words": tr.cap_len}}
+        del tr
+        torch.cuda.empty_cache()
+    return res
+
+
+def pdvc_cpu_baseline(name, seconds=20.0):
+    """The same training step on the host cores with the reference's CPU path for the two attention modules
+    (oracle/core_pytorch.module_forward = the F.grid_sample route of ms_deform_attn.py:123-124), all threads."""
+    from dense_video_captioning_b200.ops.modules import MSDeformAttn, MSDeformAttnCap
+    from dense_video_captioning_b200.pdvc import Trainer, synthetic_video
+    from oracle import core_pytorch
+    saved = MSDeformAttn.forward, MSDeformAttnCap.forward
+
+    def attn_forward(self, query, ref, src, shapes, starts, mask=None):
+        return core_pytorch.module_forward(dict(self.named_parameters()), query, ref, src, shapes, mask, self.n_heads,
+                                           self.n_levels, self.n_points)
+
+    def cap_forward(self, query, ref, src, shapes, starts, mask=None, projected_value=None):
+        return core_pytorch.module_forward(dict(self.named_parameters()), query, ref, src, shapes, mask, self.n_heads,
+                                           self.n_levels, self.n_points, caption=True)
+
+    MSDeformAttn.forward, MSDeformAttnCap.forward = attn_forward, cap_forward
+    try:
+        torch.set_num_threads(os.cpu_count() or 1)
+        tr = Trainer(name, "cpu", amp=False)
+        video = synthetic_video(tr.cfg, tr.n_gt, tr.cap_len, seed=3)
+        video = {k: v.cpu() for k, v in video.items()}
+        tr.step(video)
+        t0, n = time.perf_counter(), 0
+        while time.perf_counter() - t0 < seconds:
+            float(tr.step(video))
+            n += 1
+        dt = time.perf_counter() - t0
+        return {"value": n / dt, "unit": "videos/s", "cores": torch.get_num_threads(), "kind": "port",
+                "sample": f"{n} training steps of config {name} in {dt:.1f} s on the host cores (fp32)"}
+    finally:
+        MSDeformAttn.forward, MSDeformAttnCap.forward = saved
+
+
 def run_ours(args, world, rank, local):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py (our arm) needs a CUDA device: there is no CPU fallback for the MSDA kernels")
@@ -525,7 +601,23 @@ def run_ours(args, world, rank, local):
         "gpu_launches": launches,
         "hbm_gbs_fwd_bwd": roof["fwd_bwd"]["achieved"],
     }
+    del op
+    torch.cuda.empty_cache()
+    if not args.no_pdvc:
+        try:
+            line["pdvc_train"] = {"metric": "pdvc_train_videos_per_s", "n_gpus": world, "data": "synthetic",
+                                  "parallelism": f"ddp{world} (NCCL gradient all-reduce, 1 video per rank per step)" if world > 1
+                                  else "single process", "configs": pdvc_train_leg(args, world, rank, device)}
+        except Exception as ex:
+            if world > 1:
+                raise
+            line["pdvc_train"] = {"error": repr(ex)}
     if rank == 0:
+        if world == 1 and not args.no_cpu and not args.no_pdvc and "configs" in line.get("pdvc_train", {}):
+            try:
+                line["pdvc_train"]["cpu_baseline"] = pdvc_cpu_baseline("yc2_tsp_pdvc_yc2shape")
+            except Exception as ex:
+                line["pdvc_train"]["cpu_baseline"] = {"error": repr(ex)}
         if world == 1 and not args.no_cpu:
             cores = os.cpu_count() or 1
             torch.set_num_threads(cores)
@@ -594,6 +686,10 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extra", action="store_true")
     ap.add_argument("--sweep", default="")
+    ap.add_argument("--no-pdvc", action="store_true", help="skip the PDVC training leg")
+    ap.add_argument("--pdvc-steps", type=int, default=30)
+    ap.add_argument("--pdvc-warmup", type=int, default=5)
+    ap.add_argument("--pdvc-configs", default="", help="comma-separated subset of pdvc.CONFIGS (default: all)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.sweep:

@@ -90,7 +90,7 @@ class _MSDeformFrontEnd(nn.Module):
         return value.view(N, Len_in, self.n_heads, self.d_model // self.n_heads)
 
     def _project(self, query, reference_points, input_flatten, input_spatial_shapes, input_padding_mask,
-                 projected_value=None):
+                 projected_value=None, need_logits=True):
         """value (N,S,M,D), raw offsets and logits (N,Lq,M,L,P) -- ms_deform_attn.py:95-100."""
         if not query.is_cuda:
             raise RuntimeError("MSDeformAttn (B200 build) runs on CUDA tensors only: there is no CPU path "
@@ -103,14 +103,18 @@ class _MSDeformFrontEnd(nn.Module):
                 reference_points.shape[-1]))
         value = projected_value if projected_value is not None else self.project_value(input_flatten, input_padding_mask)
         offsets = self.sampling_offsets(query).view(N, Len_q, self.n_heads, self.n_levels, self.n_points)
-        logits = self.attention_weights(query).view(N, Len_q, self.n_heads, self.n_levels, self.n_points)
+        logits = None
+        if need_logits:
+            logits = self.attention_weights(query).view(N, Len_q, self.n_heads, self.n_levels, self.n_points)
         return value, offsets, logits
 
     def _locations_and_weights(self, reference_points, offsets, logits, input_spatial_shapes):
         """Unfused front-end (only for head dims the vectorised kernel does not take):
         ms_deform_attn.py:101-117 in torch ops on the GPU."""
         N, Len_q = offsets.shape[:2]
-        attn = F.softmax(logits.reshape(N, Len_q, self.n_heads, -1).float(), -1).view_as(logits)
+        attn = None
+        if logits is not None:
+            attn = F.softmax(logits.reshape(N, Len_q, self.n_heads, -1).float(), -1).view_as(logits).contiguous()
         offsets = offsets.float()
         if reference_points.shape[-1] == 1:
             x = reference_points[:, :, None, :, None, 0] + offsets / input_spatial_shapes[None, None, None, :, None]
@@ -118,7 +122,7 @@ class _MSDeformFrontEnd(nn.Module):
             x = reference_points[:, :, None, :, None, 0] + offsets / self.n_points * reference_points[:, :, None, :, None, 1] * 0.5
         loc = torch.stack((x, 0.5 * x.new_ones(x.shape)), -1)
         shapes2 = torch.stack([input_spatial_shapes.new_ones(input_spatial_shapes.shape), input_spatial_shapes], -1)
-        return loc.contiguous(), attn.contiguous(), shapes2.contiguous()
+        return loc.contiguous(), attn, shapes2.contiguous()
 
 
 class MSDeformAttn(_MSDeformFrontEnd):

@@ -18,8 +18,9 @@ class MSDeformAttnCap(_MSDeformFrontEnd):
     def forward(self, query, reference_points, input_flatten, input_spatial_shapes, input_level_start_index,
                 input_padding_mask=None, projected_value=None):
         value, offsets, logits = self._project(query, reference_points, input_flatten, input_spatial_shapes,
-                                               input_padding_mask, projected_value)
-        # the attention weights are computed by the reference too (:102-103) but do not reach the output
+                                               input_padding_mask, projected_value, need_logits=False)
+        # the reference computes attention weights here as well (:102-103); they never reach the output, so the
+        # projection is skipped (attention_weights / output_proj stay in the state_dict for checkpoint compatibility)
         loc, _, shapes2 = self._locations_and_weights(reference_points, offsets, logits, input_spatial_shapes)
         value = value.contiguous()
         if value.dtype != loc.dtype and value.dtype.is_floating_point and value.dtype.itemsize >= 4:

@@ -93,10 +93,13 @@ class Trainer:
         self.model, self.criterion = build(cfg)
         self.model.to(self.device).train()
         self.criterion.to(self.device)
-        # parameters the learnt-query path never touches (proposal embedding, deformable_transformer.py:136-142): without
-        # a gradient Adam skips them in the reference as well; freezing them keeps DDP's graph static
+        # parameters this training path never reaches a loss through -- the proposal embedding
+        # (deformable_transformer.py:136-142) and MSDeformAttnCap's attention_weights / output_proj
+        # (ms_deform_attn_for_caption.py:102-103: computed, never used): they have no gradient in the reference either,
+        # so Adam skips them there; freezing them keeps DDP's graph static without find_unused_parameters
         for name, p in self.model.named_parameters():
-            if name.startswith(("transformer.pos_trans.", "transformer.pos_trans_norm.")):
+            if name.startswith(("transformer.pos_trans.", "transformer.pos_trans_norm.")) or \
+                    ".core.deformable_att.attention_weights." in name or ".core.deformable_att.output_proj." in name:
                 p.requires_grad_(False)
         self.params = [p for p in self.model.parameters() if p.requires_grad]
         self.net = self.model

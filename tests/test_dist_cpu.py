@@ -43,3 +43,56 @@ def test_two_rank_sharding_and_timing_reduction():
     assert out[0][2] == out[1][2] == 11.0          # max over ranks
     assert out[0][3] == out[1][3] == 7             # shards cover the batch
     assert out[0][4] != out[1][4]                  # ranks hold different videos (rank-offset seeds)
+
+
+def _patch_cuda_modules_with_oracle():
+    """CPU stand-in for the two CUDA modules (test infrastructure; the product modules raise on CPU tensors)."""
+    from dense_video_captioning_b200.ops.modules import MSDeformAttn, MSDeformAttnCap
+    from oracle import core_pytorch
+
+    def attn_forward(self, query, ref, src, shapes, starts, mask=None):
+        return core_pytorch.module_forward(dict(self.named_parameters()), query, ref, src, shapes, mask, self.n_heads,
+                                           self.n_levels, self.n_points)
+
+    def cap_forward(self, query, ref, src, shapes, starts, mask=None, projected_value=None):
+        return core_pytorch.module_forward(dict(self.named_parameters()), query, ref, src, shapes, mask, self.n_heads,
+                                           self.n_levels, self.n_points, caption=True)
+
+    MSDeformAttn.forward = attn_forward
+    MSDeformAttnCap.forward = cap_forward
+
+
+def _ddp_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    sys.path.insert(0, ROOT)
+    torch.set_num_threads(2)
+    from dense_video_captioning_b200.pdvc import PDVCConfig, Trainer, synthetic_video
+    _patch_cuda_modules_with_oracle()
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    cfg = PDVCConfig(feature_dim=64, num_queries=6, frame_embedding_num=32, vocab_size=40, transformer_ff_dim=128,
+                     enc_layers=1, dec_layers=2, transformer_dropout_prob=0.0, drop_prob=0.0)
+    tr = Trainer(cfg, "cpu", world_size=world, lr=1e-3)
+    before = torch.cat([p.detach().flatten() for p in tr.params]).clone()
+    losses = []
+    for step in range(2):
+        video = synthetic_video(cfg, n_gt=3, cap_len=5, seed=1000 * step + rank)   # every rank its own videos
+        losses.append(float(tr.step(video)))
+    after = torch.cat([p.detach().flatten() for p in tr.params])
+    gathered = [torch.zeros_like(after) for _ in range(world)]
+    dist.all_gather(gathered, after)
+    out[rank] = (losses, float((after - before).abs().max()), float((gathered[0] - gathered[1]).abs().max()),
+                 float(before.double().sum()))
+    dist.destroy_process_group()
+
+
+def test_two_rank_ddp_training_keeps_replicas_identical():
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_ddp_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    assert out[0][3] == out[1][3]                        # identical initial weights (seeded)
+    assert out[0][0] != out[1][0]                        # different videos -> different losses
+    assert out[0][1] > 0 and out[1][1] > 0               # the step moved the parameters
+    assert out[0][2] == 0.0 and out[1][2] == 0.0         # gradient all-reduce: replicas stay bit-identical
+    assert all(l == l and abs(l) < 1e6 for l in out[0][0] + out[1][0])
