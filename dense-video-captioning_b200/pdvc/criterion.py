@@ -116,16 +116,19 @@ class SetCriterion(nn.Module):
         self.gau_mask, self.beta = gau_mask, beta
         self.register_buffer("counter_class_rate", torch.tensor(COUNTER_CLASS_RATE), persistent=False)
 
-    def _gather_index(self, indices, device):
+    @staticmethod
+    def device_indices(indices, device):
+        """Host (query_idx, target_idx) pairs -> device index tensors: (batch, query, [target per video])."""
         batch = torch.cat([torch.full_like(src, i) for i, (src, _) in enumerate(indices)]).to(device, non_blocking=True)
         src = torch.cat([src for src, _ in indices]).to(device, non_blocking=True)
-        return batch, src
+        tgt = [j.to(device, non_blocking=True) for _, j in indices]
+        return batch, src, tgt
 
-    def loss_labels(self, outputs, targets, indices, num_boxes):
+    def loss_labels(self, outputs, targets, dev_idx, sizes, num_boxes):
         logits = outputs['pred_logits']
         dev = logits.device
-        batch, src = self._gather_index(indices, dev)
-        matched = torch.cat([t["labels"][j.to(dev, non_blocking=True)] for t, (_, j) in zip(targets, indices)])
+        batch, src, tgt = dev_idx
+        matched = torch.cat([t["labels"][j] for t, j in zip(targets, tgt)])
         classes = torch.full(logits.shape[:2], self.num_classes, dtype=torch.int64, device=dev)
         classes[batch, src] = matched
         onehot = torch.zeros(logits.shape[0], logits.shape[1], logits.shape[2] + 1, dtype=logits.dtype, device=dev)
@@ -133,41 +136,47 @@ class SetCriterion(nn.Module):
         loss_ce = sigmoid_focal_loss(logits, onehot[:, :, :-1], num_boxes, self.focal_alpha, self.focal_gamma) * logits.shape[1]
         pred_count = outputs['pred_count']
         max_len = pred_count.shape[1] - 1
-        n_events = torch.tensor([min(int(t['boxes'].shape[0]), max_len) for t in targets], dtype=torch.long)
-        count_onehot = F.one_hot(n_events, max_len + 1).to(dev, non_blocking=True).to(pred_count.dtype)
+        count_onehot = torch.zeros_like(pred_count)
+        for b, t in enumerate(targets):                       # number of events is a shape: no device read
+            count_onehot[b, min(int(t['boxes'].shape[0]), max_len)].fill_(1)   # a fill kernel, not a host copy
         weight = self.counter_class_rate[:max_len + 1].to(dev)
         return {'loss_ce': loss_ce,
                 'loss_counter': counter_loss(pred_count, count_onehot, weight, self.gau_mask, self.beta)}
 
     @torch.no_grad()
-    def loss_cardinality(self, outputs, targets, indices, num_boxes):
+    def loss_cardinality(self, outputs, targets, dev_idx, sizes, num_boxes):
         logits = outputs['pred_logits']
-        want = torch.tensor([float(t["labels"].shape[0]) for t in targets]).to(logits.device, non_blocking=True)
+        want = torch.stack([torch.full((), float(t["labels"].shape[0]), device=logits.device) for t in targets])
         got = (logits.argmax(-1) != logits.shape[-1] - 1).sum(1)
         return {'cardinality_error': F.l1_loss(got.float(), want)}
 
-    def loss_boxes(self, outputs, targets, indices, num_boxes):
-        dev = outputs['pred_boxes'].device
-        batch, src = self._gather_index(indices, dev)
+    def loss_boxes(self, outputs, targets, dev_idx, sizes, num_boxes):
+        batch, src, tgt = dev_idx
         pred = outputs['pred_boxes'][batch, src]
-        want = torch.cat([t['boxes'][j.to(dev, non_blocking=True)] for t, (_, j) in zip(targets, indices)], dim=0)
+        want = torch.cat([t['boxes'][j] for t, j in zip(targets, tgt)], dim=0)
         losses = {'loss_bbox': F.l1_loss(pred, want, reduction='none').sum() / num_boxes,
                   'loss_giou': (1 - torch.diag(pairwise_giou(segments(pred), segments(want)))).sum() / num_boxes}
         # overlap among the matched predictions of each video -- logged, never weighted (criterion.py:121-129)
         overlap = torch.triu(pairwise_iou(segments(pred), segments(pred))[0], diagonal=1)
-        sizes = [len(i) for i, _ in indices]
         total = 0
         for k, cols in enumerate(overlap.split(sizes, -1)):
             total = total + cols.split(sizes, -2)[k].sum() / (0.5 * sizes[k] * (sizes[k] - 1))
         losses['loss_self_iou'] = total
         return losses
 
-    def _layer_losses(self, outputs, targets, indices, num_boxes):
+    def layer_losses(self, outputs, targets, dev_idx, sizes, num_boxes):
+        """All loss terms of one decoder layer.  dev_idx = device_indices(...) (device tensors), sizes = matched pairs per
+        video (host ints), num_boxes a host float or a 0-d device tensor: nothing here reads the device or copies from
+        the host, so the function can be captured into a CUDA graph."""
         losses = {}
-        losses.update(self.loss_labels(outputs, targets, indices, num_boxes))
-        losses.update(self.loss_boxes(outputs, targets, indices, num_boxes))
-        losses.update(self.loss_cardinality(outputs, targets, indices, num_boxes))
+        losses.update(self.loss_labels(outputs, targets, dev_idx, sizes, num_boxes))
+        losses.update(self.loss_boxes(outputs, targets, dev_idx, sizes, num_boxes))
+        losses.update(self.loss_cardinality(outputs, targets, dev_idx, sizes, num_boxes))
         return losses
+
+    def _layer_losses(self, outputs, targets, indices, num_boxes):
+        dev = outputs['pred_logits'].device
+        return self.layer_losses(outputs, targets, self.device_indices(indices, dev), [len(i) for i, _ in indices], num_boxes)
 
     def forward(self, outputs, targets):
         """-> (losses, indices of the last layer, [indices of each auxiliary layer])  (criterion.py:154-198)."""

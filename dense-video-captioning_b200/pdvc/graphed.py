@@ -1,0 +1,254 @@
+"""The PDVC training step as two CUDA graphs around the one host decision it contains.
+
+A batch-1 PDVC step is ~4 100 kernel launches for ~16 ms of device work (profiles/r1_pdvc_profile.txt): eager
+execution is bound by launch overhead (68 ms/step).  The only point where the host must see device results is the
+Hungarian assignment (scipy, pdvc/matcher.py:115-117).  So the step is split there:
+
+    stage 1  (graph)  features -> pyramid -> encoder -> decoder -> heads -> matching cost matrices of all layers
+    host              ONE read-back of the cost matrices, linear_sum_assignment per layer, indices uploaded
+    stage 2  (graph)  set losses with the matched indices + the teacher-forced caption LSTM loops -> total loss
+
+Each stage is captured once per shape key by `graph_module` below (forward graph + backward graph; the MSDeformAttn /
+MSDeformAttnCap CUDA kernels are captured like any other launch: the C ABI does no allocation and no
+synchronisation).  `total.backward()` replays stage 2's backward graph, then stage 1's; parameter gradients leave the
+graphs through autograd's AccumulateGrad, so DDP's bucketed NCCL all-reduce hooks fire as usual and overlap stage 1's
+backward with the all-reduce of the caption-head gradients.
+
+Shape key of stage 2: (events, matched pairs, word steps per layer) -- a new key is captured on first use and cached.
+`graphs=False` runs the same two stages eagerly (used by the CPU tests and as the reference for the graph tests).
+"""
+import numpy as np
+import torch
+from scipy.optimize import linear_sum_assignment
+from torch import nn
+
+from .model import caption_steps
+
+def pyramid_lengths(t0, n_levels):
+    """Level lengths of the feature pyramid: Conv1d(k3,s2,p1) per extra level (pdvc/base_encoder.py:37-41)."""
+    out = [int(t0)]
+    for _ in range(n_levels - 1):
+        out.append((out[-1] - 1) // 2 + 1)
+    return out
+
+
+def graph_module(module, sample_args, warmup=3, autocast=None):
+    """Capture `module(*sample_args)` as a forward CUDA graph and its autograd backward as a second graph; return a
+    callable with the same signature whose result is differentiable w.r.t. the tensor arguments and the module's
+    trainable parameters (the scheme of torch.cuda.make_graphed_callables, written out so that the capture runs in
+    `thread_local` error mode -- NCCL's watchdog thread may poll events while a rank is capturing -- and outputs that
+    carry no gradient are marked non-differentiable)."""
+    import contextlib
+    params = tuple(p for p in module.parameters() if p.requires_grad)
+    surface = tuple(sample_args) + params
+    diff_inputs = tuple(t for t in surface if t.requires_grad)
+    ctx = (lambda: torch.autocast("cuda", dtype=autocast, cache_enabled=False)) if autocast else contextlib.nullcontext
+
+    def run():
+        with ctx():
+            return tuple(module(*sample_args))
+
+    def backward_of(outs, grad_outs):
+        diff_outs = tuple(o for o in outs if o.requires_grad)
+        return torch.autograd.grad(diff_outs, diff_inputs, tuple(g for g in grad_outs if g is not None),
+                                   only_inputs=True, allow_unused=True)
+
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(warmup):
+            outs = run()
+            backward_of(outs, tuple(torch.ones_like(o) if o.requires_grad else None for o in outs))
+        del outs
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+
+    pool = torch.cuda.graph_pool_handle()
+    fwd_graph, bwd_graph = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+    with torch.cuda.graph(fwd_graph, pool=pool, capture_error_mode="thread_local"):
+        static_outs = run()
+    static_grad_outs = tuple(torch.zeros_like(o) if o.requires_grad else None for o in static_outs)
+    with torch.cuda.graph(bwd_graph, pool=pool, capture_error_mode="thread_local"):
+        grads = backward_of(static_outs, static_grad_outs)
+    grads = list(grads)
+    static_grad_inputs = tuple(grads.pop(0) if t.requires_grad else None for t in surface)
+    n_user = len(sample_args)
+
+    class Graphed(torch.autograd.Function):
+        @staticmethod
+        def forward(fctx, *inputs):
+            for static, new in zip(surface[:n_user], inputs[:n_user]):
+                if static.data_ptr() != new.data_ptr():
+                    static.copy_(new)
+            fwd_graph.replay()
+            outs = tuple(o.detach() for o in static_outs)
+            fctx.mark_non_differentiable(*(o for o, s in zip(outs, static_outs) if not s.requires_grad))
+            return outs
+
+        @staticmethod
+        @torch.autograd.function.once_differentiable
+        def backward(fctx, *grad_outs):
+            for static, new in zip(static_grad_outs, grad_outs):
+                if static is not None and new is not None and static.data_ptr() != new.data_ptr():
+                    static.copy_(new)
+            bwd_graph.replay()
+            return tuple(g.detach() if g is not None else None for g in static_grad_inputs)
+
+    def call(*user_args):
+        return Graphed.apply(*(tuple(user_args) + params))
+
+    call.graphs = (fwd_graph, bwd_graph)
+    # the parameters' AccumulateGrad nodes were created on the capture stream and are kept alive by the captured autograd
+    # graph; later backwards run on the caller's stream -- intended, autograd inserts the stream wait
+    quiet = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
+    if quiet is not None:
+        quiet(False)
+    return call
+
+
+LOSS_TERMS = ("loss_ce", "loss_counter", "loss_bbox", "loss_giou", "loss_self_iou", "cardinality_error", "loss_caption")
+
+
+class FeatureStage(nn.Module):
+    """Stage 1.  Tensors in: features (1,T,C), valid mask (1,T) bool, duration (1,), target segments (G,2), labels (G,)."""
+
+    def __init__(self, model, matcher):
+        super().__init__()
+        self.base_encoder = model.base_encoder
+        self.transformer = model.transformer
+        self.query_embed = model.query_embed
+        self.class_head, self.count_head, self.bbox_head = model.class_head, model.count_head, model.bbox_head
+        self.__dict__["_model"] = model          # not registered: parameters are exposed through the members above
+        self.__dict__["_matcher"] = matcher
+
+    def forward(self, vf, valid_mask, duration, tgt_boxes, tgt_labels):
+        model = self._model
+        hs, init_reference, inter_references, others = model.forward_features(vf, valid_mask, duration)
+        logits, counts, boxes = model.forward_heads(hs, init_reference, inter_references)
+        with torch.no_grad():
+            costs = torch.stack([self._matcher.cost_matrix(logits[l], boxes[l], tgt_labels, tgt_boxes)
+                                 for l in range(hs.shape[0])])
+        return (hs, init_reference, inter_references, logits, counts, boxes, others['memory'], others['mask_flatten'],
+                others['valid_ratios'], costs)
+
+
+class LossStage(nn.Module):
+    """Stage 2 for one shape key.  Everything data-dependent arrives as a device tensor; `n_steps` (word steps per
+    layer) and the pair count are fixed per instance."""
+
+    def __init__(self, model, criterion, n_steps, level_lengths):
+        super().__init__()
+        self.caption_head = model.caption_head
+        self.__dict__["_model"] = model
+        self.__dict__["_criterion"] = criterion
+        self.n_steps = tuple(n_steps)
+        self.level_lengths = list(level_lengths)
+
+    def forward(self, hs, init_reference, inter_references, logits, counts, boxes, memory, mask_flat, valid_ratios,
+                tgt_boxes, tgt_labels, cap_tensor, cap_mask, num_boxes, q_idx, t_idx):
+        model, crit = self._model, self._criterion
+        n_pred = hs.shape[0]
+        shapes, starts = model.transformer.level_tensors(self.level_lengths, hs.device)
+        others = {'memory': memory, 'mask_flatten': mask_flat, 'spatial_shapes': shapes, 'level_start_index': starts,
+                  'valid_ratios': valid_ratios, 'level_lengths': self.level_lengths}
+        targets = [{'boxes': tgt_boxes, 'labels': tgt_labels}]
+        pairs = q_idx.shape[1]
+        batch = torch.zeros(pairs, dtype=torch.long, device=hs.device)
+        terms, total = [], 0
+        for lid in range(n_pred):
+            suffix = '' if lid == n_pred - 1 else f'_{lid}'
+            out = {'pred_logits': logits[lid], 'pred_count': counts[lid], 'pred_boxes': boxes[lid]}
+            losses = crit.layer_losses(out, targets, (batch, q_idx[lid], [t_idx[lid]]), [pairs], num_boxes)
+            reference = init_reference if lid == 0 else inter_references[lid - 1]
+            head = self.caption_head[lid]
+            q, c = q_idx[lid], t_idx[lid]
+            logprobs = head(hs[lid][:, q], reference[:, q], others, cap_tensor[c], n_steps=self.n_steps[lid])
+            losses['loss_caption'] = head.build_loss(logprobs, cap_tensor[:, 1:][c], cap_mask[:, 1:][c]).mean()
+            for name in LOSS_TERMS:
+                value = losses[name]
+                terms.append(value.detach().to(torch.float64 if memory.dtype == torch.float64 else torch.float32))
+                weight = crit.weight_dict.get(name + suffix, 0)
+                if weight:
+                    total = total + (value if value.dtype == torch.float64 else value.float()) * weight
+        return total, torch.stack(terms)
+
+
+class StagedStep(nn.Module):
+    """forward(dt) -> (total loss, dict of loss terms) for ONE video, as stage 1 -> host matching -> stage 2."""
+
+    def __init__(self, model, criterion, graphs=True, amp=False):
+        super().__init__()
+        self.model = model
+        self.criterion = criterion
+        self.graphs = graphs
+        self.amp = amp
+        self.stage1 = FeatureStage(model, criterion.matcher)
+        self.__dict__["_stage1_call"] = None
+        self.__dict__["_stage2"] = {}
+        self.__dict__["_staging"] = {}
+
+    # ---- host side -------------------------------------------------------------------------------------------
+    def _match(self, costs, n_pred):
+        """One device->host transfer for all layers, then scipy's LSAP per layer (matcher.py:115-117)."""
+        host = costs.detach().float().cpu()
+        q_rows, t_rows = [], []
+        for lid in range(n_pred):
+            rows, cols = linear_sum_assignment(host[lid])
+            q_rows.append(rows)
+            t_rows.append(cols)
+        return np.stack(q_rows).astype(np.int64), np.stack(t_rows).astype(np.int64)
+
+    def _upload_indices(self, q_host, t_host, device):
+        """Pinned staging buffers (one pair per shape): indices go up with an async copy, no pageable-memory stall."""
+        if device.type != "cuda":
+            return torch.from_numpy(q_host), torch.from_numpy(t_host)
+        key = q_host.shape
+        if key not in self._staging:
+            self._staging[key] = (torch.empty(key, dtype=torch.long).pin_memory(), torch.empty(key, dtype=torch.long).pin_memory())
+        q_pin, t_pin = self._staging[key]
+        q_pin.copy_(torch.from_numpy(q_host))
+        t_pin.copy_(torch.from_numpy(t_host))
+        return q_pin.to(device, non_blocking=True), t_pin.to(device, non_blocking=True)
+
+    def _num_boxes(self, n_gt, device):
+        if torch.distributed.is_available() and torch.distributed.is_initialized():
+            total = torch.tensor([float(n_gt)], device=device)
+            torch.distributed.all_reduce(total)                      # criterion.py:169-171
+            return (total / torch.distributed.get_world_size()).clamp(min=1)[0]
+        return torch.full((), max(float(n_gt), 1.0), device=device)
+
+    def _graph(self, module, args):
+        return graph_module(module, args, autocast=torch.bfloat16 if self.amp else None)
+
+    # ---- the step --------------------------------------------------------------------------------------------
+    def forward(self, dt):
+        vf, valid, duration = dt['video_tensor'], dt['video_mask'], dt['video_length'][:, 1]
+        assert vf.shape[0] == 1, "one video per step (cfgs/*: batch_size 1; LSTM_DSA.py:59)"
+        target = dt['video_target'][0]
+        args1 = (vf, valid, duration, target['boxes'], target['labels'])
+        use_graphs = self.graphs and vf.is_cuda
+        if use_graphs and self._stage1_call is None:
+            self._stage1_call = self._graph(self.stage1, tuple(a.detach().clone() for a in args1))
+        stage1 = self._stage1_call if use_graphs else self.stage1
+        hs, init_ref, inter_refs, logits, counts, boxes, memory, mask_flat, valid_ratios, costs = stage1(*args1)
+        n_pred = hs.shape[0]
+        num_boxes = self._num_boxes(int(target['boxes'].shape[0]), vf.device)
+        q_host, t_host = self._match(costs, n_pred)
+        cap_host = dt.get('cap_tensor_host')
+        cap_host = dt['cap_tensor'].cpu().numpy() if cap_host is None else np.asarray(cap_host)
+        n_steps = tuple(caption_steps(cap_host[t_host[lid]]) for lid in range(n_pred))
+        q_idx, t_idx = self._upload_indices(q_host, t_host, vf.device)
+        args2 = (hs, init_ref, inter_refs.detach(), logits, counts, boxes, memory, mask_flat, valid_ratios.detach(),
+                 target['boxes'], target['labels'], dt['cap_tensor'], dt['cap_mask'], num_boxes, q_idx, t_idx)
+        key = (int(target['boxes'].shape[0]), q_host.shape[1], n_steps, int(vf.shape[1]), int(dt['cap_tensor'].shape[1]))
+        if key not in self._stage2:
+            lengths = pyramid_lengths(vf.shape[1], self.model.cfg.num_feature_levels)
+            stage2 = LossStage(self.model, self.criterion, n_steps, lengths)
+            if use_graphs:
+                sample = tuple(a.detach().clone().requires_grad_(a.requires_grad) for a in args2)
+                stage2 = self._graph(stage2, sample)
+            self._stage2[key] = stage2
+        total, terms = self._stage2[key](*args2)
+        names = [name + ('' if lid == n_pred - 1 else f'_{lid}') for lid in range(n_pred) for name in LOSS_TERMS]
+        return total, dict(zip(names, terms.unbind(0))), (q_host, t_host)

@@ -292,32 +292,25 @@ class PDVC(nn.Module):
             self.bbox_head = nn.ModuleList([bbox_head for _ in range(n_pred)])
             self.transformer.decoder.bbox_head = None
 
-    def forward(self, dt, criterion):
-        """dt: the reference's batch dict (data/video_dataset.py collate_fn): video_tensor (N,T,C), video_mask (N,T)
-        True = valid, video_length (N,3) [frames, seconds, n_gt], video_target [{boxes (G,2), labels (G,)}],
-        cap_tensor (G_total, words), cap_mask; optional cap_tensor_host.  Returns (outputs, loss dict)."""
-        vf = dt['video_tensor']
-        mask = ~dt['video_mask']
-        duration = dt['video_length'][:, 1]
+    def forward_features(self, vf, valid_mask, duration):
+        """Features -> pyramid -> encoder -> decoder (pdvc.py:123-157).  Tensors in, tensors out (+ `others`)."""
+        mask = ~valid_mask
         srcs, masks, pos = self.base_encoder(vf, mask, duration)
         tr = self.transformer
         src, shapes, starts, valid_ratios, pos_flat, mask_flat, lengths = tr.prepare_encoder_inputs(srcs, masks, pos)
         memory = tr.forward_encoder(src, shapes, starts, valid_ratios, pos_flat, mask_flat, lengths)
-        n = vf.shape[0]
-        query_mask = torch.ones(n, self.cfg.num_queries, dtype=torch.bool, device=vf.device)
+        query_mask = torch.ones(vf.shape[0], self.cfg.num_queries, dtype=torch.bool, device=vf.device)
         init_reference, tgt, reference_points, query_pos = tr.prepare_decoder_input_query(memory, self.query_embed.weight)
         hs, inter_references = tr.forward_decoder(tgt, reference_points, memory, shapes, starts, valid_ratios,
                                                   query_pos, mask_flat, query_mask, False)
         others = {'memory': memory, 'mask_flatten': mask_flat, 'spatial_shapes': shapes, 'level_start_index': starts,
                   'valid_ratios': valid_ratios, 'proposals_mask': query_mask, 'level_lengths': lengths}
-        return self.matched_prediction(dt, criterion, hs, init_reference, inter_references, others)
+        return hs, init_reference, inter_references, others
 
-    def matched_prediction(self, dt, criterion, hs, init_reference, inter_references, others):
-        """Heads on every decoder layer, set losses with Hungarian matching, then the caption loss of the matched
-        pairs per layer (pdvc.py:236-323)."""
-        n_pred = hs.shape[0]
-        logits, counts, boxes, references = [], [], [], []
-        for lid in range(n_pred):
+    def forward_heads(self, hs, init_reference, inter_references):
+        """Class / count / segment heads on every decoder layer (pdvc.py:246-266) -> stacked (Ld, N, ...) tensors."""
+        logits, counts, boxes = [], [], []
+        for lid in range(hs.shape[0]):
             state = hs[lid]
             reference = init_reference if lid == 0 else inter_references[lid - 1]
             delta = self.bbox_head[lid](state)
@@ -329,7 +322,22 @@ class PDVC(nn.Module):
             logits.append(self.class_head[lid](state))
             counts.append(self.count_head[lid](state.max(dim=1)[0]))
             boxes.append(delta.sigmoid())
-            references.append(reference)
+        return torch.stack(logits), torch.stack(counts), torch.stack(boxes)
+
+    def forward(self, dt, criterion):
+        """dt: the reference's batch dict (data/video_dataset.py collate_fn): video_tensor (N,T,C), video_mask (N,T)
+        True = valid, video_length (N,3) [frames, seconds, n_gt], video_target [{boxes (G,2), labels (G,)}],
+        cap_tensor (G_total, words), cap_mask; optional cap_tensor_host.  Returns (outputs, loss dict)."""
+        hs, init_reference, inter_references, others = self.forward_features(
+            dt['video_tensor'], dt['video_mask'], dt['video_length'][:, 1])
+        return self.matched_prediction(dt, criterion, hs, init_reference, inter_references, others)
+
+    def matched_prediction(self, dt, criterion, hs, init_reference, inter_references, others):
+        """Heads on every decoder layer, set losses with Hungarian matching, then the caption loss of the matched
+        pairs per layer (pdvc.py:236-323)."""
+        n_pred = hs.shape[0]
+        logits, counts, boxes = self.forward_heads(hs, init_reference, inter_references)
+        references = [init_reference if lid == 0 else inter_references[lid - 1] for lid in range(n_pred)]
         out = {'pred_logits': logits[-1], 'pred_count': counts[-1], 'pred_boxes': boxes[-1]}
         if self.cfg.aux_loss:
             out['aux_outputs'] = [{'pred_logits': logits[i], 'pred_count': counts[i], 'pred_boxes': boxes[i]}

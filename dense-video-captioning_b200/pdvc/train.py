@@ -81,7 +81,9 @@ class Trainer:
     """model + criterion + Adam(lr 5e-5, wd 1e-4) + grad clip 100 (cfgs/anet_c3d_pdvcl.yml:17,21; opts.py:104-105)."""
 
     def __init__(self, name_or_cfg, device, world_size=1, lr=5e-5, weight_decay=1e-4, grad_clip=100.0, amp=None,
-                 seed=0, dropout=None):
+                 seed=0, dropout=None, mode="graphs"):
+        """mode: 'graphs' = two CUDA graphs around the host matcher (pdvc/graphed.py; CUDA only), 'staged' = the same
+        two stages eagerly, 'eager' = the reference's control flow (model.forward with the criterion inside)."""
         spec = CONFIGS[name_or_cfg] if isinstance(name_or_cfg, str) else dict(cfg=name_or_cfg, n_gt=4, cap_len=12, amp=False)
         cfg = spec["cfg"]
         if dropout is not None:
@@ -102,14 +104,29 @@ class Trainer:
                     ".core.deformable_att.attention_weights." in name or ".core.deformable_att.output_proj." in name:
                 p.requires_grad_(False)
         self.params = [p for p in self.model.parameters() if p.requires_grad]
-        self.net = self.model
+        if mode == "graphs" and self.device.type != "cuda":
+            mode = "staged"
+        self.mode = mode
+        if self.device.type == "cuda":
+            for m in self.model.modules():
+                if isinstance(m, torch.nn.LSTM):
+                    m.flatten_parameters()
+        if mode == "eager":
+            self.net = _StepModule(self.model, self.criterion)
+        else:
+            from .graphed import StagedStep
+            self.net = StagedStep(self.model, self.criterion, graphs=(mode == "graphs"), amp=self.amp)
         if world_size > 1:
             from torch.nn.parallel import DistributedDataParallel as DDP
             ids = [self.device.index] if self.device.type == "cuda" else None
-            self.net = DDP(_StepModule(self.model, self.criterion), device_ids=ids, gradient_as_bucket_view=True,
-                           broadcast_buffers=False)
-        else:
-            self.net = _StepModule(self.model, self.criterion)
+            if self.device.type == "cuda":
+                side = torch.cuda.Stream()           # DDP built on a side stream, as graph capture inside it requires
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    self.net = DDP(self.net, device_ids=ids, gradient_as_bucket_view=True, broadcast_buffers=False)
+                torch.cuda.current_stream().wait_stream(side)
+            else:
+                self.net = DDP(self.net, gradient_as_bucket_view=True, broadcast_buffers=False)
         self.optimizer = torch.optim.Adam(self.params, lr=lr, weight_decay=weight_decay)
         self.grad_clip = grad_clip
         self.weight_dict = self.criterion.weight_dict
@@ -118,10 +135,17 @@ class Trainer:
         """One training iteration on one video; returns the (device) total loss without synchronising."""
         dt = to_device(host_batch, self.device)
         self.optimizer.zero_grad(set_to_none=True)
-        ctx = torch.autocast(self.device.type, dtype=torch.bfloat16) if self.amp else contextlib.nullcontext()
-        with ctx:
-            losses = self.net(dt)
-        total = sum(losses[k].float() * w for k, w in self.weight_dict.items() if k in losses)
+        if self.mode == "eager":
+            ctx = torch.autocast(self.device.type, dtype=torch.bfloat16) if self.amp else contextlib.nullcontext()
+            with ctx:
+                losses = self.net(dt)
+            total = sum(losses[k].float() * w for k, w in self.weight_dict.items() if k in losses)
+        else:
+            if self.amp and self.mode == "staged":
+                with torch.autocast(self.device.type, dtype=torch.bfloat16):
+                    total, losses, _ = self.net(dt)
+            else:
+                total, losses, _ = self.net(dt)       # graphs: autocast is baked into the captured stages
         total.backward()
         torch.nn.utils.clip_grad_norm_(self.params, self.grad_clip)
         self.optimizer.step()

@@ -169,6 +169,19 @@ class DeformableTransformer(nn.Module):
         nn.init.constant_(self.reference_points.bias.data, 0.)
         nn.init.normal_(self.level_embed)
 
+    def level_tensors(self, lengths, device):
+        """int64 device tensors (T_l) and (start_l) for a pyramid; cached per (lengths, device) so that steady-state
+        steps upload nothing (and the step can be captured into a CUDA graph)."""
+        cache = self.__dict__.setdefault("_level_cache", {})
+        key = (tuple(lengths), str(device))
+        if key not in cache:
+            starts = [0]
+            for t in lengths[:-1]:
+                starts.append(starts[-1] + t)
+            cache[key] = (torch.as_tensor(lengths, dtype=torch.long, device=device),
+                          torch.as_tensor(starts, dtype=torch.long, device=device))
+        return cache[key]
+
     def prepare_encoder_inputs(self, srcs, masks, pos_embeds):
         """Flatten the pyramid (deformable_transformer.py:84-114).  Also returns the level lengths as a host list:
         they are shapes, known without reading the device."""
@@ -177,11 +190,7 @@ class DeformableTransformer(nn.Module):
         mask_flatten = torch.cat(list(masks), 1)
         pos_flatten = torch.cat([p.transpose(1, 2) + self.level_embed[lvl].view(1, 1, -1)
                                  for lvl, p in enumerate(pos_embeds)], 1)
-        temporal_shapes = torch.as_tensor(lengths, dtype=torch.long, device=src_flatten.device)
-        starts = [0]
-        for t in lengths[:-1]:
-            starts.append(starts[-1] + t)
-        level_start_index = torch.as_tensor(starts, dtype=torch.long, device=src_flatten.device)
+        temporal_shapes, level_start_index = self.level_tensors(lengths, src_flatten.device)
         valid_ratios = torch.stack([(~m).sum(1).float() / m.shape[1] for m in masks], 1)
         return src_flatten, temporal_shapes, level_start_index, valid_ratios, pos_flatten, mask_flatten, lengths
 

@@ -102,6 +102,33 @@ def test_host_logic_matches_reference_model_float64(oracle_modules):
         torch.set_default_dtype(prev)
 
 
+def test_staged_step_reproduces_the_reference_losses_float64(oracle_modules):
+    """Stage 1 -> host matching -> stage 2 (pdvc/graphed.py, run eagerly on CPU) gives the reference's numbers too."""
+    from dense_video_captioning_b200.pdvc import build
+    from dense_video_captioning_b200.pdvc.graphed import StagedStep
+    golden = load_golden("pdvc_anet_c3d")
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(torch.float64)
+    try:
+        cfg = _cfg(golden)
+        model, criterion = build(cfg)
+        model.double().train()
+        cases.fill_parameters(model)
+        total, terms, (q_idx, t_idx) = StagedStep(model, criterion, graphs=False)(_batch(cfg, torch.float64, "cpu"))
+        total.backward()
+        want = dict(zip([str(n) for n in golden["loss_names"]], golden["loss_values"]))
+        assert set(want) == set(terms)
+        for k, v in want.items():
+            assert abs(float(terms[k]) - v) <= 1e-9 * max(abs(v), 1.0), k
+        assert abs(float(total) - float(golden["total_loss"])) <= 1e-9 * float(golden["total_loss"])
+        assert q_idx[-1].tolist() == golden["matched_query"].tolist()
+        norms = {cases.canonical_param_name(k): float(p.grad.norm()) for k, p in model.named_parameters() if p.grad is not None}
+        for n, norm in zip([str(x) for x in golden["grad_names"]], golden["grad_norms"]):
+            assert abs(norms[n] - norm) <= 1e-7 * max(norm, 1e-3), n
+    finally:
+        torch.set_default_dtype(prev)
+
+
 def test_state_dict_keys_follow_the_reference():
     from dense_video_captioning_b200.pdvc import PDVCConfig, build
     model, _ = build(PDVCConfig(vocab_size=50))
@@ -136,9 +163,38 @@ def test_cuda_model_matches_reference_model_fp32():
 
 
 @pytest.mark.gpu
-def test_trainer_steps_and_loss_decreases():
+def test_cuda_graph_step_matches_reference_model_fp32():
+    """The two-graph step (capture + replay) against the golden numbers of the reference model."""
+    from dense_video_captioning_b200.pdvc import build
+    from dense_video_captioning_b200.pdvc.graphed import StagedStep
+    golden = load_golden("pdvc_anet_c3d")
+    cfg = _cfg(golden)
+    model, criterion = build(cfg)
+    model.cuda().train()
+    criterion.cuda()
+    cases.fill_parameters(model)
+    step = StagedStep(model, criterion, graphs=True)
+    dt = _batch(cfg, torch.float32, "cuda")
+    want = dict(zip([str(n) for n in golden["loss_names"]], golden["loss_values"]))
+    for rep in range(3):                      # rep 0 captures, reps 1-2 replay
+        model.zero_grad(set_to_none=True)
+        total, terms, (q_idx, _) = step(dt)
+        total.backward()
+        torch.cuda.synchronize()
+        for k, v in want.items():
+            assert abs(float(terms[k]) - v) <= 2e-4 * max(abs(v), 1.0), (rep, k, float(terms[k]), v)
+        assert abs(float(total) - float(golden["total_loss"])) <= 2e-4 * float(golden["total_loss"])
+        assert q_idx[-1].tolist() == golden["matched_query"].tolist()
+        norms = {cases.canonical_param_name(k): float(p.grad.norm()) for k, p in model.named_parameters() if p.grad is not None}
+        for n, norm in zip([str(x) for x in golden["grad_names"]], golden["grad_norms"]):
+            assert abs(norms[n] - norm) <= 2e-3 * max(norm, 1e-3), (rep, n, norms[n], norm)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["eager", "staged", "graphs"])
+def test_trainer_steps_and_loss_decreases(mode):
     from dense_video_captioning_b200.pdvc import Trainer, synthetic_video
-    tr = Trainer("anet_c3d_pdvc", "cuda:0", dropout=0.0, lr=1e-4)
+    tr = Trainer("anet_c3d_pdvc", "cuda:0", dropout=0.0, lr=1e-4, mode=mode)
     video = synthetic_video(tr.cfg, tr.n_gt, tr.cap_len, seed=1)
     losses = [float(tr.step(video)) for _ in range(12)]
     assert all(np.isfinite(losses)), losses
