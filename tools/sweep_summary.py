@@ -1,0 +1,27 @@
+#!/usr/bin/env python
+"""profiles/r1_sweep.json (bench.py --sweep) -> profiles/r1_sweep_summary.md"""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+src = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "profiles", "r1_sweep.json")
+d = json.load(open(src))
+rows, peak = d["rows"], d["peak_gbs"]
+out = [f"# BASELINE configs[4] sweep (bench.py --sweep), B200, fused boundary, HBM peak {peak:.0f} GB/s (MEASURED_PEAKS.json)", "",
+       "`frac` = algorithmic bytes of fwd+bwd (every tensor counted once, DESIGN.md section 4) / time / peak.  M=8, D=64, L=4.",
+       "Encoder rows (Lq = S) read every value row, so `frac` is a true HBM fraction.  **Decoder rows (Lq = 100) sample only",
+       "100 x 8 x L x P x 2 of the S x 8 value rows per video**: the forward never touches most of `value`, so its algorithmic-byte",
+       "figure over-counts real traffic and can exceed the peak (e.g. 7.6 TB/s 'achieved' at N=256, T0=2000); the backward still",
+       "writes all of `grad_value`.  Decoder `frac` is listed for completeness, not as a bandwidth claim.", ""]
+for kind in ("encoder", "decoder"):
+    for dtype in ("f32", "bf16"):
+        out += [f"## {kind}, {dtype}", "", "| N | T0 | S | P | fwd us | bwd us | Mqueries/s | fwd GB/s | bwd GB/s | frac |", "|---|---|---|---|---|---|---|---|---|---|"]
+        for r in sorted((r for r in rows if r["kind"] == kind and r["dtype"] == dtype), key=lambda r: (r["P"], r["T0"], r["N"])):
+            out.append(f"| {r['N']} | {r['T0']} | {r['S']} | {r['P']} | {r['fwd_us']:.1f} | {r['bwd_us']:.1f} | {r['queries_per_s'] / 1e6:.2f} | "
+                       f"{r['fwd_gbs']:.0f} | {r['bwd_gbs']:.0f} | {r['fwd_bwd_frac_hbm']:.3f} |")
+        out.append("")
+open(os.path.join(ROOT, "profiles", "r1_sweep_summary.md"), "w").write("\n".join(out))
+enc = [r for r in rows if r["kind"] == "encoder"]
+best = max(enc, key=lambda r: r["fwd_bwd_frac_hbm"])
+print(len(rows), "rows; best encoder point:", best)
