@@ -427,3 +427,28 @@ def test_full_size_properties(dvc, dtype):
     v64 = _np64(w["value"][:1])
     want = O.fused_forward(v64, T, _np64(w["ref"][:1, q0:q1]), _np64(w["off"][:1, q0:q1]), _np64(w["logits"][:1, q0:q1]), O.BORDER)
     _assert_close(_np64(out[:1, q0:q1]), want, dtype, "full/out-slice")
+
+
+def test_host_pipeline_equals_single_call(dvc):
+    """ops/host_pipeline.HostPipelinedFusedMSDA (chunks on three streams, pinned host tensors in and out) returns what one
+    fused call on the whole batch returns: chunking the batch is pure scheduling.  Uneven last chunk included."""
+    import bench
+    from dense_video_captioning_b200.ops.host_pipeline import HostPipelinedFusedMSDA
+    w = bench.make_workload(11, 64, 8, 64, 4, 4, "encoder", "cuda", seed=21)
+    v = w["value"].clone().requires_grad_(True)
+    o = w["off"].clone().requires_grad_(True)
+    lg = w["logits"].clone().requires_grad_(True)
+    out = dvc.MSDeformAttnFusedFunction.apply(v, w["shapes"], w["lsi"], w["ref"], o, lg, "border")
+    out.backward(w["grad_out"])
+    torch.cuda.synchronize()
+    host = [w[k].cpu().pin_memory() for k in ("value", "ref", "off", "logits", "grad_out")]
+    pipe = HostPipelinedFusedMSDA(w["shapes"], w["lsi"], "cuda", chunk=4)
+    for _ in range(2):      # second run reuses the buffers
+        got = pipe.run(*host)
+        torch.cuda.synchronize()
+    assert torch.equal(got[0], out.detach().cpu())
+    assert torch.equal(got[2], o.grad.cpu()) and torch.equal(got[3], lg.grad.cpu())
+    # grad_value is accumulated with float atomics: equal up to summation order
+    assert float((got[1] - v.grad.cpu()).abs().max()) <= 1e-5 * float(v.grad.abs().max())
+    with pytest.raises(RuntimeError):
+        pipe.run(*[t.cuda() for t in host])
