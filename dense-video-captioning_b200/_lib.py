@@ -33,6 +33,8 @@ SIGNATURES = {
     "msda_fused_backward": (_i, [_vp] * 11 + [_vp, _sz] + [_i] * 8 + [_i, _i, _u, _vp]),
     "msda_sample_forward": (_i, [_vp] * 5 + [_i] * 7 + [_i, _i, _u, _vp]),
     "msda_sample_backward": (_i, [_vp] * 7 + [_vp, _sz] + [_i] * 7 + [_i, _i, _u, _vp]),
+    "msda_cap_sample_forward": (_i, [_vp] * 6 + [_i] * 8 + [_i, _i, _u, _vp]),
+    "msda_cap_sample_backward": (_i, [_vp] * 9 + [_vp, _sz] + [_i] * 8 + [_i, _i, _u, _vp]),
 }
 
 _lib = None

@@ -12,6 +12,7 @@
 #include "msda_generic.cuh"
 #include "msda_tile.cuh"
 #include "msda_lean.cuh"
+#include "msda_capsample.cuh"
 
 using namespace msda;
 
@@ -680,6 +681,75 @@ int msda_sample_forward(const void *value, const int64_t *spatial_shapes, const 
     a.assume_1d = (flags & MSDA_FLAG_ASSUME_1D) ? 1 : 0;
     a.total = (long long)N * Lq * M * D;
     return launch_generic_fwd<true>(a, dtype, static_cast<cudaStream_t>(stream));
+}
+
+int msda_cap_sample_forward(const void *value, const int64_t *temporal_shapes, const int64_t *level_start_index,
+                            const float *reference_points, const float *sampling_offsets, void *samples, int N, int S,
+                            int M, int D, int L, int Lq, int P, int R, int dtype, int pad_mode, unsigned flags, void *stream)
+{
+    (void)flags;
+    g_launches = 0;
+    const Dims d{N, S, M, D, L, Lq, P};
+    if (int e = check_dims(d, dtype, pad_mode)) return e;
+    if (R != 1 && R != 2) return MSDA_ERR_SHAPE;
+    if (!value || !temporal_shapes || !level_start_index || !reference_points || !sampling_offsets || !samples) return MSDA_ERR_NULL;
+    if (!aligned16(value) || !aligned16(samples)) return MSDA_ERR_ALIGN;
+    const int ch = dtype == MSDA_BF16 ? 8 : 4;
+    if (dtype == MSDA_F64 || D % ch) return MSDA_ERR_UNSUPPORTED;
+    CapArgs a{};
+    a.value = value; a.shapes = temporal_shapes; a.lsi = level_start_index; a.ref = reference_points;
+    a.off = sampling_offsets; a.samples = samples;
+    a.N = N; a.S = S; a.M = M; a.D = D; a.L = L; a.Lq = Lq; a.P = P; a.R = R; a.pad_mode = pad_mode;
+    a.total = (long long)N * Lq * M * L * P * (D / ch);
+    long long blocks = (a.total + 255) / 256;
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dtype == MSDA_F32) msda_cap_fwd_kernel<float><<<(int)blocks, 256, 0, st>>>(a);
+    else msda_cap_fwd_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, st>>>(a);
+    return check_launch();
+}
+
+int msda_cap_sample_backward(const void *value, const int64_t *temporal_shapes, const int64_t *level_start_index,
+                             const float *reference_points, const float *sampling_offsets, const void *grad_samples,
+                             void *grad_value, float *grad_reference_points, float *grad_sampling_offsets,
+                             void *workspace, size_t workspace_bytes, int N, int S, int M, int D, int L, int Lq, int P,
+                             int R, int dtype, int pad_mode, unsigned flags, void *stream)
+{
+    (void)flags;
+    g_launches = 0;
+    const Dims d{N, S, M, D, L, Lq, P};
+    if (int e = check_dims(d, dtype, pad_mode)) return e;
+    if (R != 1 && R != 2) return MSDA_ERR_SHAPE;
+    if (!value || !temporal_shapes || !level_start_index || !reference_points || !sampling_offsets || !grad_samples ||
+        !grad_value || !grad_sampling_offsets)
+        return MSDA_ERR_NULL;
+    if (!aligned16(value) || !aligned16(grad_samples) || !aligned16(grad_value)) return MSDA_ERR_ALIGN;
+    const int ch = dtype == MSDA_BF16 ? 8 : 4;
+    if (dtype == MSDA_F64 || D % ch) return MSDA_ERR_UNSUPPORTED;
+    const size_t need = msda_backward_workspace_bytes(N, S, M, D, dtype);
+    if (need && (!workspace || workspace_bytes < need || !aligned16(workspace))) return MSDA_ERR_WORKSPACE;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const long long nv = (long long)N * S * M * D;
+    const long long ns = (long long)N * Lq * M * L * P;
+    void *acc = dtype == MSDA_BF16 ? workspace : grad_value;
+    if (int e = memset_async(acc, (size_t)nv * 4, st)) return e;
+    if (int e = memset_async(grad_sampling_offsets, (size_t)ns * 4, st)) return e;
+    if (grad_reference_points)
+        if (int e = memset_async(grad_reference_points, (size_t)N * Lq * L * R * 4, st)) return e;
+    CapArgs a{};
+    a.value = value; a.shapes = temporal_shapes; a.lsi = level_start_index; a.ref = reference_points;
+    a.off = sampling_offsets; a.grad_samples = grad_samples;
+    a.gv_acc = static_cast<float *>(acc); a.grad_ref = grad_reference_points; a.grad_off = grad_sampling_offsets;
+    a.N = N; a.S = S; a.M = M; a.D = D; a.L = L; a.Lq = Lq; a.P = P; a.R = R; a.pad_mode = pad_mode;
+    a.total = ns * (D / ch);
+    // grid-stride with whole-warp liveness: the grid covers `total` in full rounds of the same stride
+    long long blocks = (a.total + 255) / 256;
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    if (dtype == MSDA_F32) msda_cap_bwd_kernel<float><<<(int)blocks, 256, 0, st>>>(a);
+    else msda_cap_bwd_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, st>>>(a);
+    if (int rc = check_launch()) return rc;
+    if (dtype == MSDA_BF16) return finish_bf16(static_cast<const float *>(acc), grad_value, nv, st);
+    return MSDA_OK;
 }
 
 int msda_sample_backward(const void *value, const int64_t *spatial_shapes, const int64_t *level_start_index,

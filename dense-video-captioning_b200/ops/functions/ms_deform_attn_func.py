@@ -316,6 +316,72 @@ class MSDeformSampleFunction(Function):
         return grad_value, None, None, grad_loc, None, None
 
 
+class MSDeformCapSampleFunction(Function):
+    """apply(value, temporal_shapes, level_start_index, reference_points, sampling_offsets, padding_mode=None)
+    -> un-weighted samples in the kernel's layout (N, Lq, M, L*P, D).
+
+    Fused front-end of MSDeformAttnCap (ms_deform_attn_for_caption.py:100-123) for the 1-D temporal case: locations
+    from reference points + raw offsets, dummy y, sampling -- one kernel forward, one backward.  The reference's
+    (N*M, D, Lq, L, P) tensor is `out.view(N, Lq, M, L, P, D).permute(0, 2, 5, 1, 3, 4).reshape(N*M, D, Lq, L, P)`."""
+
+    @staticmethod
+    def supported(value):
+        ch = 8 if value.dtype == torch.bfloat16 else 4
+        return value.dtype in (torch.float32, torch.bfloat16) and value.shape[-1] % ch == 0
+
+    @staticmethod
+    def forward(ctx, value, temporal_shapes, level_start_index, reference_points, sampling_offsets, padding_mode=None):
+        _check_cuda_contig(value=value, temporal_shapes=temporal_shapes, level_start_index=level_start_index,
+                           reference_points=reference_points, sampling_offsets=sampling_offsets)
+        _require(value.dtype in (torch.float32, torch.bfloat16), "fused sampler takes float32 or bfloat16 values")
+        _require(temporal_shapes.dtype == torch.int64 and temporal_shapes.dim() == 1, "temporal_shapes must be (L,) int64")
+        _require(reference_points.dtype == torch.float32 and sampling_offsets.dtype == torch.float32,
+                 "reference_points and sampling_offsets must be float32")
+        N, S, M, D = value.shape
+        _require(sampling_offsets.dim() == 5, "sampling_offsets must be (N, Lq, M, L, P)")
+        _, Lq, M2, L, P = sampling_offsets.shape
+        R = reference_points.shape[-1]
+        _require(M2 == M and sampling_offsets.shape[0] == N, "sampling_offsets does not match value")
+        _require(tuple(reference_points.shape) == (N, Lq, L, R), "reference_points must be (N, Lq, L, R)")
+        if R not in (1, 2):
+            raise ValueError(f"Last dim of reference_points must be 1 or 2, but get {R} instead.")
+        pad = _pad_code(padding_mode)
+        out = torch.empty((N, Lq, M, L * P, D), dtype=value.dtype, device=value.device)
+        with torch.cuda.device(value.device):
+            rc = _lib.lib().msda_cap_sample_forward(
+                _ptr(value), _ptr(temporal_shapes), _ptr(level_start_index), _ptr(reference_points),
+                _ptr(sampling_offsets), _ptr(out), N, S, M, D, L, Lq, P, R, _DTYPES[value.dtype], pad, 0,
+                _stream(value.device))
+        _lib.check(rc, "msda_cap_sample_forward")
+        ctx.pad = pad
+        ctx.save_for_backward(value, temporal_shapes, level_start_index, reference_points, sampling_offsets)
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, grad_samples):
+        value, shapes, lsi, ref, off = ctx.saved_tensors
+        N, S, M, D = value.shape
+        _, Lq, _, L, P = off.shape
+        R = ref.shape[-1]
+        grad_samples = grad_samples.contiguous()
+        _require(grad_samples.dtype == value.dtype, "grad_samples dtype must match value")
+        grad_value = torch.empty_like(value)
+        grad_off = torch.empty_like(off)
+        grad_ref = torch.empty_like(ref) if ctx.needs_input_grad[3] else None
+        lib = _lib.lib()
+        code = _DTYPES[value.dtype]
+        ws_bytes = lib.msda_backward_workspace_bytes(N, S, M, D, code)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=value.device) if ws_bytes else None
+        with torch.cuda.device(value.device):
+            rc = lib.msda_cap_sample_backward(
+                _ptr(value), _ptr(shapes), _ptr(lsi), _ptr(ref), _ptr(off), _ptr(grad_samples), _ptr(grad_value),
+                _ptr(grad_ref), _ptr(grad_off), _ptr(ws), ws_bytes, N, S, M, D, L, Lq, P, R, code, ctx.pad, 0,
+                _stream(value.device))
+        _lib.check(rc, "msda_cap_sample_backward")
+        return grad_value, None, None, grad_ref, grad_off, None
+
+
 def ms_deform_attn_core_pytorch(value, value_spatial_shapes, sampling_locations, attention_weights,
                                 return_value=False):
     """Same call as the reference helper (func.py:41-68): no level_start_index argument, optional

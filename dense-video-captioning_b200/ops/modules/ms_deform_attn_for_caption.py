@@ -4,7 +4,7 @@ Same front-end as MSDeformAttn on a 2*d_model query (hidden state + event featur
 LSTM, pdvc/CaptioningHead/LSTM_DSA.py:239-240); returns the raw sampled values (N*M, D, Lq, L, P) with
 no weighting and no output projection (ms_deform_attn_for_caption.py:120-123).  The reference always
 takes the F.grid_sample path here, even on CUDA; this module runs the sampler CUDA kernel."""
-from ..functions.ms_deform_attn_func import MSDeformSampleFunction
+from ..functions.ms_deform_attn_func import MSDeformCapSampleFunction, MSDeformSampleFunction
 from .ms_deform_attn import _MSDeformFrontEnd
 
 
@@ -19,6 +19,17 @@ class MSDeformAttnCap(_MSDeformFrontEnd):
                 input_padding_mask=None, projected_value=None):
         value, offsets, logits = self._project(query, reference_points, input_flatten, input_spatial_shapes,
                                                input_padding_mask, projected_value, need_logits=False)
+        value = value.contiguous()
+        if MSDeformCapSampleFunction.supported(value):
+            # one fused kernel each way (csrc/msda_capsample.cuh); the reference's (N*M, D, Lq, L, P) is returned as a
+            # permuted view of the kernel's (N, Lq, M, L*P, D) buffer: same shape, same values, D-contiguous memory
+            N, Lq = offsets.shape[:2]
+            M, L, P, D = self.n_heads, self.n_levels, self.n_points, value.shape[-1]
+            samples = MSDeformCapSampleFunction.apply(
+                value, input_spatial_shapes.contiguous(), input_level_start_index.contiguous(),
+                reference_points.float().contiguous(), offsets.float().contiguous(), self.padding_mode)
+            return samples.view(N, Lq, M, L, P, D).permute(0, 2, 5, 1, 3, 4).reshape(N * M, D, Lq, L, P)
+        # head dims the vectorised kernel does not take: torch front-end + generic sampler kernel.
         # the reference computes attention weights here as well (:102-103); they never reach the output, so the
         # projection is skipped (attention_weights / output_proj stay in the state_dict for checkpoint compatibility)
         loc, _, shapes2 = self._locations_and_weights(reference_points, offsets, logits, input_spatial_shapes)

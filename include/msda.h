@@ -161,6 +161,31 @@ int msda_sample_backward(const void *value, const int64_t *spatial_shapes,
                          void *workspace, size_t workspace_bytes, int N, int S, int M, int D, int L,
                          int Lq, int P, int dtype, int pad_mode, unsigned flags, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Fused caption sampler: everything MSDeformAttnCap.forward does between its Linear projections and
+ * its return for the 1-D temporal case (pdvc/ops/modules/ms_deform_attn_for_caption.py:100-123:
+ * sampling locations from reference points + raw offsets, dummy y, ms_deform_attn_core_pytorch with
+ * return_value=True) in one kernel each way.  f32 / bf16, D a multiple of 4 (f32) or 8 (bf16).
+ *   reference_points (N,Lq,L,R) f32, R in {1,2};  sampling_offsets (N,Lq,M,L,P) f32 (raw Linear output)
+ *   samples / grad_samples  (N, Lq, M, L*P, D)  -- D contiguous; the reference's (N*M, D, Lq, L, P)
+ *                           is the permutation (0,2,4,1,3) of this buffer
+ *   grad_value (N,S,M,D), grad_sampling_offsets, grad_reference_points (NULL to skip) overwritten.
+ *   workspace: msda_backward_workspace_bytes(N,S,M,D,dtype) bytes (bf16 only).
+ * ------------------------------------------------------------------------------------------- */
+int msda_cap_sample_forward(const void *value, const int64_t *temporal_shapes,
+                            const int64_t *level_start_index, const float *reference_points,
+                            const float *sampling_offsets, void *samples, int N, int S, int M, int D,
+                            int L, int Lq, int P, int R, int dtype, int pad_mode, unsigned flags,
+                            void *stream);
+
+int msda_cap_sample_backward(const void *value, const int64_t *temporal_shapes,
+                             const int64_t *level_start_index, const float *reference_points,
+                             const float *sampling_offsets, const void *grad_samples,
+                             void *grad_value, float *grad_reference_points,
+                             float *grad_sampling_offsets, void *workspace, size_t workspace_bytes,
+                             int N, int S, int M, int D, int L, int Lq, int P, int R, int dtype,
+                             int pad_mode, unsigned flags, void *stream);
+
 /* Number of kernels the last call on this thread launched (bench.py's gpu_launches). */
 int msda_last_launch_count(void);
 

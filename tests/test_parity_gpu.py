@@ -452,3 +452,76 @@ def test_host_pipeline_equals_single_call(dvc):
     assert float((got[1] - v.grad.cpu()).abs().max()) <= 1e-5 * float(v.grad.abs().max())
     with pytest.raises(RuntimeError):
         pipe.run(*[t.cuda() for t in host])
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("pad", ["border", "zeros"])
+@pytest.mark.parametrize("shape", [(1, 1, 512, 6, 4, 1), (1, 1, 512, 6, 4, 2), (3, 4, 32, 17, 8, 1), (2, 2, 24, 5, 3, 2)],
+                         ids=["cap_R1", "cap_R2", "n3_m4_d32_p8", "n2_m2_d24_p3_R2"])
+def test_fused_caption_sampler_vs_oracle(dvc, shape, pad, dtype):
+    """msda_cap_sample_forward/backward (csrc/msda_capsample.cuh): samples, grad_value, grad_offsets and
+    grad_reference_points against the oracle's sampler + the chain rule of ms_deform_attn_for_caption.py:104-112."""
+    from dense_video_captioning_b200.ops.functions import MSDeformCapSampleFunction
+    N, M, D, Lq, P, R = shape
+    if dtype == torch.bfloat16 and D % 8:
+        pytest.skip("bf16 vector path needs D % 8 == 0")
+    T = cases.level_lengths(200)
+    L, S = len(T), sum(T)
+    rs = np.random.RandomState(3)
+    value = torch.from_numpy(rs.standard_normal((N, S, M, D))).to(dtype)
+    ref = rs.uniform(0.05, 0.95, (N, Lq, L, R)).astype(np.float32)
+    if R == 2:
+        ref[..., 1] = rs.uniform(0.05, 0.3, (N, Lq, L))
+    off = (rs.standard_normal((N, Lq, M, L, P)) * 3).astype(np.float32)
+    x = O.sampling_locations(ref, off, T, P)
+    x = cases.keep_off_knots(x, T)                       # move the offsets so that locations stay off the knots
+    Tl = np.asarray(T, dtype=np.float64)[None, None, None, :, None]
+    scale = (1.0 / Tl) if R == 1 else (ref[:, :, None, :, None, 1].astype(np.float64) * 0.5 / P)
+    off = ((x - ref[:, :, None, :, None, 0]) / scale).astype(np.float32)
+    gs = torch.from_numpy(rs.standard_normal((N, Lq, M, L * P, D))).to(dtype)
+    dev = "cuda"
+    tv = value.to(dev).requires_grad_(True)
+    tr = torch.from_numpy(ref).to(dev).requires_grad_(True)
+    to = torch.from_numpy(off).to(dev).requires_grad_(True)
+    shp = torch.tensor(T, dtype=torch.long, device=dev)
+    lsi = torch.cat((shp.new_zeros((1,)), shp.cumsum(0)[:-1]))
+    out = MSDeformCapSampleFunction.apply(tv, shp, lsi, tr, to, pad)
+    out.backward(gs.to(dev))
+    torch.cuda.synchronize()
+    # oracle: exact fp64 on the values the kernel saw
+    v64 = _np64(value)
+    x64 = O.sampling_locations(ref, off, T, P)
+    loc = np.stack([x64, np.full_like(x64, 0.5)], -1)
+    attn = np.full((N, Lq, M, L, P), 1.0)
+    _, want = O.forward(v64, T, loc, attn, PAD[pad], return_samples=True)       # (N*M, D, Lq, L, P)
+    want_k = want.reshape(N, M, D, Lq, L * P).transpose(0, 3, 1, 4, 2)           # kernel layout (N, Lq, M, LP, D)
+    gs_ref = _np64(gs).reshape(N, Lq, M, L, P, D).transpose(0, 2, 5, 1, 3, 4).reshape(N * M, D, Lq, L, P)
+    gv, gl = O.sample_backward(v64, T, loc, np.ascontiguousarray(gs_ref), PAD[pad])
+    gx = gl[..., 0]
+    g_off = gx * scale
+    g_ref = np.zeros(ref.shape)
+    g_ref[..., 0] = gx.sum(axis=(2, 4))
+    if R == 2:
+        g_ref[..., 1] = (gx * off.astype(np.float64) * 0.5 / P).sum(axis=(2, 4))
+    _assert_close(_np64(out), want_k, dtype, "samples")
+    _assert_close(_np64(tv.grad), gv, dtype, "grad_value", rel_scale=2.0)
+    for name, got, ref_arr in (("grad_offsets", to.grad, g_off), ("grad_reference_points", tr.grad, g_ref)):
+        d = np.abs(_np64(got) - ref_arr)
+        rel, ab = TOL[dtype]
+        bad = float((d > 4 * rel * np.abs(ref_arr).max() + ab).mean())
+        assert bad <= 2e-3, f"{name}: {bad:.2e} of elements differ"
+
+
+def test_caption_module_returns_reference_shape_as_view(dvc):
+    """MSDeformAttnCap keeps the reference's output shape (N*M, D, Lq, L, P); for the caption head (N = M = 1) it is a
+    view of the kernel's D-contiguous buffer, and the head's own permute (LSTM_DSA.py:241-242) is contiguous again."""
+    m = dvc.MSDeformAttnCap(512, 4, 1, 4).cuda()
+    T = torch.tensor(cases.level_lengths(100), device="cuda")
+    lsi = torch.cat((T.new_zeros((1,)), T.cumsum(0)[:-1]))
+    q = torch.randn(1, 6, 1024, device="cuda")
+    src = torch.randn(1, int(T.sum()), 512, device="cuda")
+    ref = torch.rand(1, 6, 4, 1, device="cuda")
+    out = m(q, ref, src, T, lsi)
+    assert tuple(out.shape) == (1, 512, 6, 4, 4)
+    back = out.reshape(1, 1, 512, 6, 16).permute(0, 3, 1, 4, 2)
+    assert back.is_contiguous()
