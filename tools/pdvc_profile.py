@@ -13,9 +13,41 @@ from dense_video_captioning_b200.pdvc import Trainer, synthetic_video  # noqa: E
 from dense_video_captioning_b200.pdvc.train import to_device  # noqa: E402
 
 
+def graph_mode_profile(tr):
+    """Two-graph step: device time by kernel under replay, plus the host-visible phases."""
+    from torch.profiler import ProfilerActivity, profile
+    video = synthetic_video(tr.cfg, tr.n_gt, tr.cap_len, seed=1)
+    for _ in range(6):
+        tr.step(video)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(20):
+        float(tr.step(video))
+    torch.cuda.synchronize()
+    print(f"{tr.mode}: {(time.perf_counter() - t0) / 20 * 1e3:.2f} ms/step")
+    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+        for _ in range(3):
+            float(tr.step(video))
+        torch.cuda.synchronize()
+    ev = prof.key_averages()
+    kernels = [e for e in ev if e.device_type == torch.autograd.DeviceType.CUDA]
+    n_launch = sum(e.count for e in kernels) / 3
+    dev_ms = sum(e.device_time_total for e in kernels) / 3e3
+    print(f"kernel nodes per step: {n_launch:.0f}, summed device time {dev_ms:.2f} ms/step")
+    for e in sorted(kernels, key=lambda e: -e.device_time_total)[:40]:
+        print(f"  {e.count / 3:7.1f} x {e.device_time_total / 3e3:8.3f} ms  {e.key[:120]}")
+    cpu_ops = sorted([e for e in ev if e.device_type == torch.autograd.DeviceType.CPU], key=lambda e: -e.self_cpu_time_total)[:15]
+    print("top host ops (self cpu, per step):")
+    for e in cpu_ops:
+        print(f"  {e.count / 3:7.1f} x {e.self_cpu_time_total / 3e3:8.3f} ms  {e.key[:100]}")
+
+
 def main():
     name = sys.argv[1] if len(sys.argv) > 1 else "yc2_tsp_pdvc_yc2shape"
-    tr = Trainer(name, "cuda:0")
+    mode = sys.argv[2] if len(sys.argv) > 2 else "eager"
+    tr = Trainer(name, "cuda:0", mode=mode)
+    if mode != "eager":
+        return graph_mode_profile(tr)
     video = synthetic_video(tr.cfg, tr.n_gt, tr.cap_len, seed=1)
     for _ in range(5):
         tr.step(video)
