@@ -17,6 +17,8 @@ backward with the all-reduce of the caption-head gradients.
 Shape key of stage 2: (events, matched pairs, word steps per layer) -- a new key is captured on first use and cached.
 `graphs=False` runs the same two stages eagerly (used by the CPU tests and as the reference for the graph tests).
 """
+import contextlib
+
 import numpy as np
 import torch
 from scipy.optimize import linear_sum_assignment
@@ -144,6 +146,13 @@ class LossStage(nn.Module):
         self.__dict__["_criterion"] = criterion
         self.n_steps = tuple(n_steps)
         self.level_lengths = list(level_lengths)
+        self.parallel_layers = True
+        self.__dict__["_streams"] = []
+
+    def _side_streams(self, n, device):
+        while len(self._streams) < n:
+            self._streams.append(torch.cuda.Stream(device))
+        return self._streams[:n]
 
     def forward(self, hs, init_reference, inter_references, logits, counts, boxes, memory, mask_flat, valid_ratios,
                 tgt_boxes, tgt_labels, cap_tensor, cap_mask, num_boxes, q_idx, t_idx):
@@ -155,16 +164,48 @@ class LossStage(nn.Module):
         targets = [{'boxes': tgt_boxes, 'labels': tgt_labels}]
         pairs = q_idx.shape[1]
         batch = torch.zeros(pairs, dtype=torch.long, device=hs.device)
+
+        # The caption loops of the decoder layers are independent chains of ~1 300 tiny kernels each: on the GPU every
+        # layer's loop runs on its own stream (inside a capture these become parallel branches of the graph, forward and --
+        # because autograd replays each node on the stream it ran on -- backward).  cuDNN's RNN calls serialise across
+        # streams in host issue order (tools/graph_fork_probe.py), so the word steps of the layers are issued in lockstep:
+        # the branches then wait for each other only at the LSTM cell and overlap everywhere else.
+        n_side = n_pred - 1 if (hs.is_cuda and self.parallel_layers) else 0
+        main = torch.cuda.current_stream() if n_side else None
+        side = self._side_streams(n_side, hs.device) if n_side else []
+
+        def on_stream(lid):
+            return torch.cuda.stream(side[lid - 1]) if (n_side and lid > 0) else contextlib.nullcontext()
+
+        for s_ in side:
+            s_.wait_stream(main)
+        decoders = []
+        for lid in range(n_pred):
+            with on_stream(lid):
+                reference = init_reference if lid == 0 else inter_references[lid - 1]
+                q, c = q_idx[lid], t_idx[lid]
+                decoders.append(self.caption_head[lid].prepare(hs[lid][:, q], reference[:, q], others, cap_tensor[c]))
+        for i in range(max(self.n_steps)):
+            for lid in range(n_pred):
+                if i < self.n_steps[lid]:
+                    with on_stream(lid):
+                        decoders[lid].step(i)
+        cap = []
+        for lid in range(n_pred):
+            with on_stream(lid):
+                c = t_idx[lid]
+                cap.append(self.caption_head[lid].build_loss(decoders[lid].result(), cap_tensor[:, 1:][c], cap_mask[:, 1:][c]).mean())
+        set_losses = []
+        for lid in range(n_pred):
+            out = {'pred_logits': logits[lid], 'pred_count': counts[lid], 'pred_boxes': boxes[lid]}
+            set_losses.append(crit.layer_losses(out, targets, (batch, q_idx[lid], [t_idx[lid]]), [pairs], num_boxes))
+        for s_ in side:
+            main.wait_stream(s_)
         terms, total = [], 0
         for lid in range(n_pred):
             suffix = '' if lid == n_pred - 1 else f'_{lid}'
-            out = {'pred_logits': logits[lid], 'pred_count': counts[lid], 'pred_boxes': boxes[lid]}
-            losses = crit.layer_losses(out, targets, (batch, q_idx[lid], [t_idx[lid]]), [pairs], num_boxes)
-            reference = init_reference if lid == 0 else inter_references[lid - 1]
-            head = self.caption_head[lid]
-            q, c = q_idx[lid], t_idx[lid]
-            logprobs = head(hs[lid][:, q], reference[:, q], others, cap_tensor[c], n_steps=self.n_steps[lid])
-            losses['loss_caption'] = head.build_loss(logprobs, cap_tensor[:, 1:][c], cap_mask[:, 1:][c]).mean()
+            losses = set_losses[lid]
+            losses['loss_caption'] = cap[lid]
             for name in LOSS_TERMS:
                 value = losses[name]
                 terms.append(value.detach().to(torch.float64 if memory.dtype == torch.float64 else torch.float32))

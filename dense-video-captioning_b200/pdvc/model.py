@@ -233,14 +233,46 @@ class LSTMDSACaptioner(nn.Module):
         seq = cap_tensor.long()
         if n_steps is None:
             n_steps = caption_steps(seq.cpu().numpy())
-        pairs = hs.shape[1]
-        state = (hs.new_zeros(self.num_layers, pairs, self.rnn_size), hs.new_zeros(self.num_layers, pairs, self.rnn_size))
-        value = core.deformable_att.project_value(memory, mask).contiguous()   # once per sentence, not per word
-        outputs = []
+        decoder = self.begin(hs, ref, memory, shapes, starts, mask, seq)
         for i in range(n_steps):
-            out, state = core(self.embed(seq[:, i]), state, hs, ref, memory, shapes, starts, mask, projected_value=value)
-            outputs.append(F.log_softmax(self.logit(self.dropout(out)), dim=1))
-        return torch.stack(outputs, 1)
+            decoder.step(i)
+        return decoder.result()
+
+    def prepare(self, hs, reference, others, cap_tensor):
+        """Everything `forward` does before its word loop, as a SentenceDecoder whose steps the caller drives (the
+        two-graph trainer interleaves the word steps of all decoder layers across streams, pdvc/graphed.py)."""
+        assert self.core.n_levels == others['spatial_shapes'].shape[0], "level-truncated caption heads go through forward()"
+        valid = others['valid_ratios']
+        if reference.shape[-1] == 2:
+            ref = reference[:, :, None] * torch.stack([valid, valid], -1)[:, None]
+        else:
+            ref = reference[:, :, None] * valid[:, None, :, None]
+        return self.begin(hs, ref, others['memory'], others['spatial_shapes'], others['level_start_index'],
+                          others['mask_flatten'], cap_tensor.long())
+
+    def begin(self, hs, ref, memory, shapes, starts, mask, seq):
+        return SentenceDecoder(self, hs, ref, memory, shapes, starts, mask, seq)
+
+
+class SentenceDecoder:
+    """State of one teacher-forced decoding run: LSTM state, projected memory, log-probabilities so far."""
+
+    def __init__(self, head, hs, ref, memory, shapes, starts, mask, seq):
+        self.head, self.hs, self.ref, self.memory, self.shapes, self.starts, self.mask, self.seq = (
+            head, hs, ref, memory, shapes, starts, mask, seq)
+        pairs = hs.shape[1]
+        self.state = (hs.new_zeros(head.num_layers, pairs, head.rnn_size), hs.new_zeros(head.num_layers, pairs, head.rnn_size))
+        self.value = head.core.deformable_att.project_value(memory, mask).contiguous()   # once per sentence, not per word
+        self.outputs = []
+
+    def step(self, i):
+        head = self.head
+        out, self.state = head.core(head.embed(self.seq[:, i]), self.state, self.hs, self.ref, self.memory, self.shapes,
+                                    self.starts, self.mask, projected_value=self.value)
+        self.outputs.append(F.log_softmax(head.logit(head.dropout(out)), dim=1))
+
+    def result(self):
+        return torch.stack(self.outputs, 1)
 
 
 def caption_steps(seq_host):
