@@ -241,11 +241,11 @@ template <bool FUSED, bool BWD> int launch_tile(const TileArgs &a, const TilePla
                              : launch_tile_lanes<__nv_bfloat16, FUSED, BWD>(a, p, grid, st);
 }
 
-// ---- lean kernels (L*P <= 32): planning and launch ---------------------------------------------------
+// ---- lean kernels (L*P <= 64): planning and launch ---------------------------------------------------
 
 struct LeanPlan {
     bool ok;
-    int lpg, nch, lpa, Q, chunks, win_rows, gridK;
+    int lpg, nch, lpa, spl, Q, chunks, win_rows, gridK;
     size_t smem;
 };
 
@@ -258,7 +258,7 @@ LeanPlan lean_plan(const Dims &d, int dtype, bool backward)
     if (!use_lean || dtype == MSDA_F64) return p;
     const int LP = d.L * d.P;
     const int rb = d.D * (dtype == MSDA_BF16 ? 2 : 4);
-    if (LP > 32 || rb % 16 != 0) return p;
+    if (LP > 64 || rb % 16 != 0) return p;   // lane j of a unit's group owns samples j, j + 32 (spl = 2) when L*P > 32
     const int chunks16 = rb / 16;
     if (chunks16 == 4) { p.lpg = 4; p.nch = 1; }
     else if (chunks16 == 8 || chunks16 == 16 || chunks16 == 32) { p.lpg = 8; p.nch = chunks16 / 8; }
@@ -266,11 +266,12 @@ LeanPlan lean_plan(const Dims &d, int dtype, bool backward)
     if (d.N > 65535 || d.M > 65535 || d.S >= (1 << 26)) return p;
     if ((long long)d.N * d.Lq * d.M * LP >= (1ll << 30)) return p;   // 32-bit sample indices
     p.lpa = LP <= 16 ? 16 : 32;
+    p.spl = LP > 32 ? 2 : 1;
     const int upp = kLeanWarps * (32 / p.lpa);
-    int passes = kLeanPasses;
+    int passes = kLeanPasses / p.spl;
     // small problems: fewer queries per CTA so that every SM gets work
     while (passes > 1 && (long long)d.N * d.M * ((d.Lq + upp * passes - 1) / (upp * passes)) < 2 * kNumSMs) passes >>= 1;
-    if (passes_env > 0 && passes_env <= kLeanPasses) passes = passes_env;
+    if (passes_env > 0 && passes_env <= kLeanPasses / p.spl) passes = passes_env;
     p.Q = upp * passes;
     p.chunks = (d.Lq + p.Q - 1) / p.Q;
     // self-attention (the queries are the rows of the level pyramid): tile by time span, see tile_queries()
@@ -283,14 +284,14 @@ LeanPlan lean_plan(const Dims &d, int dtype, bool backward)
         static const int bwin_kb = env_int("MSDA_BWIN_KB", 34);
         p.win_rows = bwin_kb * 1024 / rb;
         if (p.win_rows > d.S + d.L) p.win_rows = d.S + d.L;
-        p.smem = bwd_lean_smem_bytes(p.Q, p.lpa, d.S, rb, p.win_rows);
+        p.smem = bwd_lean_smem_bytes(p.Q, p.lpa * p.spl, d.S, rb, p.win_rows);
         if (p.smem > kMaxDynSmem) {   // no room for a window: gather value rows through L1
             p.win_rows = 0;
-            p.smem = bwd_lean_smem_bytes(p.Q, p.lpa, d.S, rb, 0);
+            p.smem = bwd_lean_smem_bytes(p.Q, p.lpa * p.spl, d.S, rb, 0);
         }
         if (p.smem > kMaxDynSmem) return p;
     } else {
-        const size_t recs = (size_t)p.Q * p.lpa * sizeof(int4);
+        const size_t recs = (size_t)p.Q * p.lpa * p.spl * sizeof(int4);
         const size_t win = (size_t)win_kb * 1024;
         p.win_rows = (int)(win / rb);
         if (p.win_rows > d.S) p.win_rows = d.S;   // the whole head slice fits
@@ -314,17 +315,17 @@ void fill_lean_args(TileArgs &a, const Dims &d, const LeanPlan &p, int pad_mode)
     a.gridK = p.gridK;
 }
 
-template <typename VT, int LPG, int NCH, int LPA, bool FUSED, bool BWD>
+template <typename VT, int LPG, int NCH, int LPA, bool FUSED, bool BWD, int SPL = 1>
 int launch_lean_inst(const TileArgs &a, const LeanPlan &p, cudaStream_t st)
 {
     static unsigned long long done = 0;
     const dim3 grid(p.chunks, a.M, a.N);
     if (BWD) {
-        if (int e = allow_big_smem(msda_bwd_lean_kernel<VT, LPG, NCH, LPA, FUSED>, done)) return e;
-        msda_bwd_lean_kernel<VT, LPG, NCH, LPA, FUSED><<<grid, kLeanThreads, p.smem, st>>>(a);
+        if (int e = allow_big_smem(msda_bwd_lean_kernel<VT, LPG, NCH, LPA, FUSED, SPL>, done)) return e;
+        msda_bwd_lean_kernel<VT, LPG, NCH, LPA, FUSED, SPL><<<grid, kLeanThreads, p.smem, st>>>(a);
     } else {
-        if (int e = allow_big_smem(msda_fwd_lean_kernel<VT, LPG, NCH, LPA, FUSED>, done)) return e;
-        msda_fwd_lean_kernel<VT, LPG, NCH, LPA, FUSED><<<grid, kLeanThreads, p.smem, st>>>(a);
+        if (int e = allow_big_smem(msda_fwd_lean_kernel<VT, LPG, NCH, LPA, FUSED, SPL>, done)) return e;
+        msda_fwd_lean_kernel<VT, LPG, NCH, LPA, FUSED, SPL><<<grid, kLeanThreads, p.smem, st>>>(a);
     }
     return check_launch();
 }
@@ -334,7 +335,8 @@ template <typename VT, bool FUSED, bool BWD> int launch_lean_shape(const TileArg
 #define MSDA_LEAN_CASE(LPG_, NCH_)                                                                       \
     if (p.lpg == LPG_ && p.nch == NCH_)                                                                  \
         return p.lpa == 16 ? launch_lean_inst<VT, LPG_, NCH_, 16, FUSED, BWD>(a, p, st)                  \
-                           : launch_lean_inst<VT, LPG_, NCH_, 32, FUSED, BWD>(a, p, st);
+             : p.spl == 1  ? launch_lean_inst<VT, LPG_, NCH_, 32, FUSED, BWD>(a, p, st)                  \
+                           : launch_lean_inst<VT, LPG_, NCH_, 32, FUSED, BWD, 2>(a, p, st);
 #ifndef MSDA_DEV_FAST   // development builds instantiate the headline shape only
     MSDA_LEAN_CASE(4, 1)
     MSDA_LEAN_CASE(8, 1)

@@ -3,7 +3,7 @@
 // Same algorithm as msda_tile.cuh (chunk of Q queries of one head per CTA; forward = value window staged
 // in shared memory by cp.async.bulk + LDS.128 gather; backward = samples counting-sorted by value row, one
 // lane group per row), re-written for instruction economy after ncu showed both tile kernels issue-bound
-// (profiles/r1_notes.md): every lane decodes at most ONE sample per query (L*P <= 32), so level, T_l,
+// (profiles/r1_notes.md): every lane decodes ONE sample per query (L*P <= 32; two, SPL = 2, up to L*P = 64), so level, T_l,
 // level start are per-lane constants, all indices are 32-bit, decoded samples stay in registers between
 // phases, each lane owns NCH 16-byte chunks of a value row (fewer shuffle steps per dot product and
 // fewer address computations per FFMA2).
@@ -159,17 +159,14 @@ struct Decoded {
     float dxdoff;    // fused: d(loc)/d(offset)
 };
 
-// softmax over the LPA lanes of a unit's group (FUSED) + sampling geometry; all lanes of the warp call it
-template <bool FUSED, int LPA>
-__device__ __forceinline__ Decoded decode(const TileArgs &a, const LaneLevel &c, const RawSample &raw, bool on)
+// sampling geometry of one sample given its attention weight
+template <bool FUSED>
+__device__ __forceinline__ Decoded decode_geom(const TileArgs &a, const LaneLevel &c, const RawSample &raw, float A)
 {
     Decoded d;
     float hi, lo;
+    d.A = A;
     if (FUSED) {
-        const float mx = group_max<LPA>(on ? raw.y : -INFINITY);
-        const float e = on ? __expf(raw.y - mx) : 0.f;
-        const float sum = group_sum<LPA>(e);
-        d.A = sum > 0.f ? __fdividef(e, sum) : 0.f;
         const float p = raw.r0 * c.tf;
         const float plo = fmaf(raw.r0, c.tf, -p);
         float add;
@@ -184,7 +181,6 @@ __device__ __forceinline__ Decoded decode(const TileArgs &a, const LaneLevel &c,
         two_sum(p, add, hi, err);
         lo = plo + err;
     } else {
-        d.A = raw.y;
         d.dxdoff = 0.f;
         pix_from_loc(raw.x, c.T, hi, lo);
     }
@@ -193,6 +189,35 @@ __device__ __forceinline__ Decoded decode(const TileArgs &a, const LaneLevel &c,
     d.r1 = c.start + t.i1;
     d.w0 = t.w0; d.w1 = t.w1; d.s0 = t.s0; d.s1 = t.s1;
     return d;
+}
+
+// softmax over the L*P samples of a unit (FUSED): LPA lanes x SPL samples per lane (lane j owns samples j + s*LPA),
+// then the geometry of every sample; all lanes of the warp call it
+template <bool FUSED, int LPA, int SPL>
+__device__ __forceinline__ void decode(const TileArgs &a, const LaneLevel (&c)[SPL], const RawSample (&raw)[SPL],
+                                       const bool (&on)[SPL], Decoded (&d)[SPL])
+{
+    float A[SPL];
+    if (FUSED) {
+        float m = -INFINITY;
+#pragma unroll
+        for (int s = 0; s < SPL; ++s) m = fmaxf(m, on[s] ? raw[s].y : -INFINITY);
+        const float mx = group_max<LPA>(m);
+        float e[SPL], part = 0.f;
+#pragma unroll
+        for (int s = 0; s < SPL; ++s) {
+            e[s] = on[s] ? __expf(raw[s].y - mx) : 0.f;
+            part += e[s];
+        }
+        const float sum = group_sum<LPA>(part);
+#pragma unroll
+        for (int s = 0; s < SPL; ++s) A[s] = sum > 0.f ? __fdividef(e[s], sum) : 0.f;
+    } else {
+#pragma unroll
+        for (int s = 0; s < SPL; ++s) A[s] = raw[s].y;
+    }
+#pragma unroll
+    for (int s = 0; s < SPL; ++s) d[s] = decode_geom<FUSED>(a, c[s], raw[s], A[s]);
 }
 
 // value / grad rows: lane j of a row group owns the 16-byte chunks c*LPG + j, c < NCH
@@ -234,7 +259,7 @@ template <typename VT, int LPG, int NCH> struct RowIO {
 // ---------------------------------------------------------------------------------------------
 // forward.  grid = (chunks, M, N); dynamic shared memory = [ records int4 x Q*LPA | value window ]
 // ---------------------------------------------------------------------------------------------
-template <typename VT, int LPG, int NCH, int LPA, bool FUSED>
+template <typename VT, int LPG, int NCH, int LPA, bool FUSED, int SPL = 1>
 __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileArgs a)
 {
     using IO = RowIO<VT, LPG, NCH>;
@@ -243,7 +268,9 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
     constexpr int G = 32 / LPG;     // units per warp in the gather phase
     constexpr int UPW = 32 / LPA;   // units per warp in the decode phase
     constexpr int UPP = kLeanWarps * UPW;
-    constexpr int QMAX = UPP * kLeanPasses;
+    constexpr int PASSES = kLeanPasses / SPL;   // SPL samples per lane (32 < L*P <= 64): half the units per lane
+    constexpr int LPT = LPA * SPL;              // sample slots per unit
+    constexpr int QMAX = UPP * PASSES;
     extern __shared__ __align__(128) unsigned char dsm[];
     MSDA_PHASE_DECL
     __shared__ int win_lo[kMaxLevels], win_hi[kMaxLevels], win_base[kMaxLevels];
@@ -256,48 +283,62 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
     const int MD = a.M * a.D;
     constexpr int rb = LPG * NCH * 16;   // bytes per row of one head (= D * sizeof(VT))
     int4 *recs = reinterpret_cast<int4 *>(dsm);
-    unsigned char *win = dsm + (size_t)a.Q * LPA * sizeof(int4);
+    unsigned char *win = dsm + (size_t)a.Q * LPT * sizeof(int4);
 
     if (tid < a.L) { win_lo[tid] = INT_MAX; win_hi[tid] = -1; }
     if (a.gridK) tile_runs_init(a, blockIdx.x, runs);
     __syncthreads();   // win_lo / win_hi / mbar / runs initialised
     MSDA_PHASE_MARK
 
-    // ---- decode: lane (g, j) handles sample j of units warp*UPW + g + t*UPP, t < passes ----
+    // ---- decode: lane (g, j) handles samples j + s*LPA of units warp*UPW + g + t*UPP, t < passes ----
     const int g1 = lane / LPA, j1 = lane % LPA;
-    const LaneLevel lc = lane_level(a, j1);
-    int ulv[kLeanPasses], qv[kLeanPasses];
+    LaneLevel lc[SPL];
 #pragma unroll
-    for (int t = 0; t < kLeanPasses; ++t) ulv[t] = t * UPP + warp * UPW + g1;
-    const int Qc = tile_queries<kLeanPasses>(a, blockIdx.x, runs, ulv, qv);
+    for (int s = 0; s < SPL; ++s) lc[s] = lane_level(a, j1 + s * LPA);
+    int ulv[PASSES], qv[PASSES];
+#pragma unroll
+    for (int t = 0; t < PASSES; ++t) ulv[t] = t * UPP + warp * UPW + g1;
+    const int Qc = tile_queries<PASSES>(a, blockIdx.x, runs, ulv, qv);
     const int passes = (Qc + UPP - 1) / UPP;
-    RawSample raw[kLeanPasses];
+    RawSample raw[PASSES][SPL];
 #pragma unroll
-    for (int t = 0; t < kLeanPasses; ++t) {
-        const bool on = lc.live && qv[t] >= 0;
+    for (int t = 0; t < PASSES; ++t) {
         const int nq = n * a.Lq + (qv[t] >= 0 ? qv[t] : 0);
-        raw[t] = load_raw<FUSED>(a, lc, nq, (nq * a.M + m) * a.LP + j1, on);
+#pragma unroll
+        for (int s = 0; s < SPL; ++s) {
+            const bool on = lc[s].live && qv[t] >= 0;
+            raw[t][s] = load_raw<FUSED>(a, lc[s], nq, (nq * a.M + m) * a.LP + j1 + s * LPA, on);
+        }
         if (j1 == 0 && ulv[t] < a.Q) uq[ulv[t]] = qv[t];
     }
-    int r0[kLeanPasses], r1[kLeanPasses];
-    float c0[kLeanPasses], c1[kLeanPasses];
-    int lo = INT_MAX, hi = -1;
+    int r0[PASSES][SPL], r1[PASSES][SPL];
+    float c0[PASSES][SPL], c1[PASSES][SPL];
+    int lo[SPL], hi[SPL];
 #pragma unroll
-    for (int t = 0; t < kLeanPasses; ++t) {
-        r0[t] = r1[t] = -1;
-        c0[t] = c1[t] = 0.f;
+    for (int s = 0; s < SPL; ++s) { lo[s] = INT_MAX; hi[s] = -1; }
+#pragma unroll
+    for (int t = 0; t < PASSES; ++t) {
+#pragma unroll
+        for (int s = 0; s < SPL; ++s) { r0[t][s] = r1[t][s] = -1; c0[t][s] = c1[t][s] = 0.f; }
         if (t < passes) {   // block-uniform
-            const bool on = lc.live && qv[t] >= 0;
-            const Decoded d = decode<FUSED, LPA>(a, lc, raw[t], on);
-            const float k0 = d.A * d.w0, k1 = d.A * d.w1;
-            if (on && (k0 != 0.f || k1 != 0.f)) {
-                r0[t] = d.r0; r1[t] = d.r1; c0[t] = k0; c1[t] = k1;
-                lo = min(lo, d.r0);
-                hi = max(hi, d.r1);
+            bool on[SPL];
+#pragma unroll
+            for (int s = 0; s < SPL; ++s) on[s] = lc[s].live && qv[t] >= 0;
+            Decoded d[SPL];
+            decode<FUSED, LPA, SPL>(a, lc, raw[t], on, d);
+#pragma unroll
+            for (int s = 0; s < SPL; ++s) {
+                const float k0 = d[s].A * d[s].w0, k1 = d[s].A * d[s].w1;
+                if (on[s] && (k0 != 0.f || k1 != 0.f)) {
+                    r0[t][s] = d[s].r0; r1[t][s] = d[s].r1; c0[t][s] = k0; c1[t][s] = k1;
+                    lo[s] = min(lo[s], d[s].r0);
+                    hi[s] = max(hi[s], d[s].r1);
+                }
             }
         }
     }
-    window_update(win_lo, win_hi, lc.l, lo, hi);
+#pragma unroll
+    for (int s = 0; s < SPL; ++s) window_update(win_lo, win_hi, lc[s].l, lo[s], hi[s]);
     __syncthreads();
     MSDA_PHASE_MARK
     if (tid == 0) {
@@ -328,14 +369,18 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
         }
     }
     {   // final records: byte offsets into the window (staged) or element offsets into the slice
-        const int base = staged ? win_base[lc.l] : 0;
         const int scale = staged ? rb : MD;
 #pragma unroll
-        for (int t = 0; t < kLeanPasses; ++t) {
+        for (int t = 0; t < PASSES; ++t) {
             if (t < passes && ulv[t] < Qc) {
-                const bool livet = r0[t] >= 0;
-                recs[ulv[t] * LPA + (j1 ^ rec_swizzle(ulv[t]))] = make_int4(livet ? (base + r0[t]) * scale : 0, livet ? (base + r1[t]) * scale : 0,
-                                                    __float_as_int(c0[t]), __float_as_int(c1[t]));
+#pragma unroll
+                for (int s = 0; s < SPL; ++s) {
+                    const int base = staged ? win_base[lc[s].l] : 0;
+                    const bool livet = r0[t][s] >= 0;
+                    recs[ulv[t] * LPT + s * LPA + (j1 ^ rec_swizzle(ulv[t]))] =
+                        make_int4(livet ? (base + r0[t][s]) * scale : 0, livet ? (base + r1[t][s]) * scale : 0,
+                                  __float_as_int(c0[t][s]), __float_as_int(c1[t][s]));
+                }
             }
         }
     }
@@ -354,7 +399,7 @@ __global__ void __launch_bounds__(kLeanThreads) msda_fwd_lean_kernel(const TileA
         for (int ul0 = warp * G; ul0 < Qc; ul0 += kLeanWarps * G) {
             const int ul = ul0 + g;
             const bool active = ul < Qc;
-            const int4 *rp = recs + (active ? ul : 0) * LPA;
+            const int4 *rp = recs + (active ? ul : 0) * LPT;
             const int sw = rec_swizzle(active ? ul : 0);
             float acc[NF];
 #pragma unroll
@@ -408,7 +453,7 @@ __host__ __device__ inline size_t bwd_lean_smem_bytes(int Q, int LPA, int S, int
     return (size_t)Q * rb + (2 * QS + 2) * 16 + (QS + 1 + 1) * 8 + ((size_t)S + 1 + 3) / 4 * 16 + (size_t)win_rows * rb;
 }
 
-template <typename VT, int LPG, int NCH, int LPA, bool FUSED>
+template <typename VT, int LPG, int NCH, int LPA, bool FUSED, int SPL = 1>
 __global__ void __launch_bounds__(kLeanThreads, MSDA_BWD_MINB) msda_bwd_lean_kernel(const TileArgs a)
 {
     using IO = RowIO<VT, LPG, NCH>;
@@ -417,7 +462,9 @@ __global__ void __launch_bounds__(kLeanThreads, MSDA_BWD_MINB) msda_bwd_lean_ker
     constexpr int NG = kLeanThreads / LPG;   // row groups per CTA
     constexpr int UPW = 32 / LPA;
     constexpr int UPP = kLeanWarps * UPW;
-    constexpr int QMAX = UPP * kLeanPasses;
+    constexpr int PASSES = kLeanPasses / SPL;   // SPL samples per lane (32 < L*P <= 64): half the units per lane
+    constexpr int LPT = LPA * SPL;              // sample slots per unit
+    constexpr int QMAX = UPP * PASSES;
     constexpr int rb = LPG * NCH * 16;
     extern __shared__ __align__(128) unsigned char dsm[];
     MSDA_PHASE_DECL
@@ -430,7 +477,7 @@ __global__ void __launch_bounds__(kLeanThreads, MSDA_BWD_MINB) msda_bwd_lean_ker
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int n = blockIdx.z, m = blockIdx.y;
     const int MD = a.M * a.D;
-    const int QS = a.Q * LPA;
+    const int QS = a.Q * LPT;
     unsigned char *Gs = dsm;
     int4 *ent = reinterpret_cast<int4 *>(Gs + (size_t)a.Q * rb);
     float2 *dots = reinterpret_cast<float2 *>(ent + 2 * QS + 2);
@@ -445,48 +492,66 @@ __global__ void __launch_bounds__(kLeanThreads, MSDA_BWD_MINB) msda_bwd_lean_ker
 
     // ---- raw inputs of this lane's samples ----
     const int g1 = lane / LPA, j1 = lane % LPA;
-    const LaneLevel lc = lane_level(a, j1);
-    int ulv[kLeanPasses], qv[kLeanPasses];
+    LaneLevel lc[SPL];
 #pragma unroll
-    for (int t = 0; t < kLeanPasses; ++t) ulv[t] = t * UPP + warp * UPW + g1;
-    const int Qc = tile_queries<kLeanPasses>(a, blockIdx.x, runs, ulv, qv);
+    for (int s = 0; s < SPL; ++s) lc[s] = lane_level(a, j1 + s * LPA);
+    int ulv[PASSES], qv[PASSES];
+#pragma unroll
+    for (int t = 0; t < PASSES; ++t) ulv[t] = t * UPP + warp * UPW + g1;
+    const int Qc = tile_queries<PASSES>(a, blockIdx.x, runs, ulv, qv);
     const int passes = (Qc + UPP - 1) / UPP;
-    RawSample raw[kLeanPasses];
+    RawSample raw[PASSES][SPL];
 #pragma unroll
-    for (int t = 0; t < kLeanPasses; ++t) {
-        const bool on = lc.live && qv[t] >= 0;
+    for (int t = 0; t < PASSES; ++t) {
         const int nq = n * a.Lq + (qv[t] >= 0 ? qv[t] : 0);
-        raw[t] = load_raw<FUSED>(a, lc, nq, (nq * a.M + m) * a.LP + j1, on);
+#pragma unroll
+        for (int s = 0; s < SPL; ++s) {
+            const bool on = lc[s].live && qv[t] >= 0;
+            raw[t][s] = load_raw<FUSED>(a, lc[s], nq, (nq * a.M + m) * a.LP + j1 + s * LPA, on);
+        }
         if (j1 == 0 && ulv[t] < a.Q) uq[ulv[t]] = qv[t];
     }
 
     // ---- decode; per-level range of first rows ----
-    int key[kLeanPasses], rank[kLeanPasses];
-    float wa[kLeanPasses], wb[kLeanPasses], ga[kLeanPasses], gb[kLeanPasses], At[kLeanPasses], dxd[kLeanPasses];
-    bool two[kLeanPasses];
-    int lo = INT_MAX, hi = -1;
+    int key[PASSES][SPL], rank[PASSES][SPL];
+    float wa[PASSES][SPL], wb[PASSES][SPL], ga[PASSES][SPL], gb[PASSES][SPL], At[PASSES][SPL], dxd[PASSES][SPL];
+    bool two[PASSES][SPL];
+    int lo[SPL], hi[SPL];
 #pragma unroll
-    for (int t = 0; t < kLeanPasses; ++t) {
-        key[t] = -1; rank[t] = 0; two[t] = false;
-        wa[t] = wb[t] = ga[t] = gb[t] = At[t] = dxd[t] = 0.f;
+    for (int s = 0; s < SPL; ++s) { lo[s] = INT_MAX; hi[s] = -1; }
+#pragma unroll
+    for (int t = 0; t < PASSES; ++t) {
+#pragma unroll
+        for (int s = 0; s < SPL; ++s) {
+            key[t][s] = -1; rank[t][s] = 0; two[t][s] = false;
+            wa[t][s] = wb[t][s] = ga[t][s] = gb[t][s] = At[t][s] = dxd[t][s] = 0.f;
+        }
         if (t < passes) {   // block-uniform
-            const bool on = lc.live && qv[t] >= 0;
-            const Decoded d = decode<FUSED, LPA>(a, lc, raw[t], on);
-            if (on) {
-                float xa = d.w0, xb = d.w1, sa = d.s0, sb = d.s1;
-                if (d.r1 == d.r0) { xa += xb; sa += sb; xb = 0.f; sb = 0.f; }   // one row only
-                const float at = d.A * lc.tf;
-                wa[t] = xa; wb[t] = xb; ga[t] = sa * at; gb[t] = sb * at; At[t] = d.A; dxd[t] = d.dxdoff;
-                if (xa != 0.f || xb != 0.f || sa != 0.f || sb != 0.f) {
-                    key[t] = d.r0;
-                    two[t] = xb != 0.f || sb != 0.f;
-                    lo = min(lo, d.r0);
-                    hi = max(hi, d.r0);
+            bool on[SPL];
+#pragma unroll
+            for (int s = 0; s < SPL; ++s) on[s] = lc[s].live && qv[t] >= 0;
+            Decoded dd[SPL];
+            decode<FUSED, LPA, SPL>(a, lc, raw[t], on, dd);
+#pragma unroll
+            for (int s = 0; s < SPL; ++s) {
+                const Decoded &d = dd[s];
+                if (on[s]) {
+                    float xa = d.w0, xb = d.w1, sa = d.s0, sb = d.s1;
+                    if (d.r1 == d.r0) { xa += xb; sa += sb; xb = 0.f; sb = 0.f; }   // one row only
+                    const float at = d.A * lc[s].tf;
+                    wa[t][s] = xa; wb[t][s] = xb; ga[t][s] = sa * at; gb[t][s] = sb * at; At[t][s] = d.A; dxd[t][s] = d.dxdoff;
+                    if (xa != 0.f || xb != 0.f || sa != 0.f || sb != 0.f) {
+                        key[t][s] = d.r0;
+                        two[t][s] = xb != 0.f || sb != 0.f;
+                        lo[s] = min(lo[s], d.r0);
+                        hi[s] = max(hi[s], d.r0);
+                    }
                 }
             }
         }
     }
-    window_update(win_lo, win_hi, lc.l, lo, hi);
+#pragma unroll
+    for (int s = 0; s < SPL; ++s) window_update(win_lo, win_hi, lc[s].l, lo[s], hi[s]);
     __syncthreads();   // uq, win_lo / win_hi complete
     MSDA_PHASE_MARK
 
@@ -500,17 +565,25 @@ __global__ void __launch_bounds__(kLeanThreads, MSDA_BWD_MINB) msda_bwd_lean_ker
         }
     }
     // compact row index of slice row r at level l: wbase_l + r; tot = rows in all level windows (<= S)
-    int tot = 0, my_base = 0;
+    int tot = 0, my_base[SPL];
+#pragma unroll
+    for (int s = 0; s < SPL; ++s) my_base[s] = 0;
     for (int l = 0; l < a.L; ++l) {
         const int wl = win_lo[l], wh = win_hi[l];
-        if (l == lc.l) my_base = tot - wl;
+#pragma unroll
+        for (int s = 0; s < SPL; ++s)
+            if (l == lc[s].l) my_base[s] = tot - wl;
         if (wh >= wl) tot += wh - wl + 1;
     }
     for (int i = tid; i <= tot; i += kLeanThreads) start[i] = 0;
     // value window: rows [lo_l, hi_l + 1] of every touched level (first rows and their second taps), cp.async
-    int vtot = 0, my_vbase = 0;
+    int vtot = 0, my_vbase[SPL];
+#pragma unroll
+    for (int s = 0; s < SPL; ++s) my_vbase[s] = 0;
     for (int l = 0; l < a.L; ++l) {
-        if (l == lc.l) my_vbase = vtot - win_lo[l];
+#pragma unroll
+        for (int s = 0; s < SPL; ++s)
+            if (l == lc[s].l) my_vbase[s] = vtot - win_lo[l];
         vtot += win_hi[l] >= win_lo[l] ? win_hi[l] - win_lo[l] + 2 : 0;
     }
     const bool vstaged = vtot <= a.win_rows;
@@ -534,8 +607,10 @@ __global__ void __launch_bounds__(kLeanThreads, MSDA_BWD_MINB) msda_bwd_lean_ker
 
     // ---- histogram of first rows ----
 #pragma unroll
-    for (int t = 0; t < kLeanPasses; ++t) {
-        if (key[t] >= 0) rank[t] = atomicAdd(&start[my_base + key[t]], 1);
+    for (int t = 0; t < PASSES; ++t) {
+#pragma unroll
+        for (int s = 0; s < SPL; ++s)
+            if (key[t][s] >= 0) rank[t][s] = atomicAdd(&start[my_base[s] + key[t][s]], 1);
     }
     __syncthreads();
     MSDA_PHASE_MARK
@@ -580,12 +655,15 @@ __global__ void __launch_bounds__(kLeanThreads, MSDA_BWD_MINB) msda_bwd_lean_ker
 
     // ---- scatter samples into row order ----
 #pragma unroll
-    for (int t = 0; t < kLeanPasses; ++t) {
-        if (key[t] >= 0) {
-            const int ul = ulv[t];
-            ent[start[my_base + key[t]] + rank[t]] =
-                make_int4((ul * LPA + j1) | (two[t] ? 0x8000 : 0) | ((my_vbase + key[t]) << 16), __float_as_int(At[t] * wa[t]),
-                          __float_as_int(At[t] * wb[t]), key[t]);
+    for (int t = 0; t < PASSES; ++t) {
+#pragma unroll
+        for (int s = 0; s < SPL; ++s) {
+            if (key[t][s] >= 0) {
+                const int ul = ulv[t];
+                ent[start[my_base[s] + key[t][s]] + rank[t][s]] =
+                    make_int4((ul * LPT + s * LPA + j1) | (two[t][s] ? 0x8000 : 0) | ((my_vbase[s] + key[t][s]) << 16),
+                              __float_as_int(At[t][s] * wa[t][s]), __float_as_int(At[t][s] * wb[t][s]), key[t][s]);
+            }
         }
     }
     cp_async_commit_wait_all();
@@ -655,7 +733,7 @@ __global__ void __launch_bounds__(kLeanThreads, MSDA_BWD_MINB) msda_bwd_lean_ker
             }
             any1 = any1 || ((e0.x | e1.x) & 0x8000) != 0;
             float gq0[NF], gq1[NF];
-            int u0 = (e0.x & 0x7fff) / LPA, u1 = (e1.x & 0x7fff) / LPA;   // no-op entries (slot QS) read unit 0
+            int u0 = (e0.x & 0x7fff) / LPT, u1 = (e1.x & 0x7fff) / LPT;   // no-op entries (slot QS) read unit 0
             u0 = u0 < a.Q ? u0 : 0;
             u1 = u1 < a.Q ? u1 : 0;
             IO::load_smem(glane + u0 * rb, gq0);
@@ -685,49 +763,58 @@ __global__ void __launch_bounds__(kLeanThreads, MSDA_BWD_MINB) msda_bwd_lean_ker
     {
         const bool p_pow2 = (a.P & (a.P - 1)) == 0 && a.P <= LPA;
 #pragma unroll
-        for (int t = 0; t < kLeanPasses; ++t) {
+        for (int t = 0; t < PASSES; ++t) {
             if (t < passes) {   // block-uniform
                 const int ul = ulv[t];
-                const bool on = lc.live && qv[t] >= 0;
                 const int nq = n * a.Lq + (qv[t] >= 0 ? qv[t] : 0);
-                const int sidx = (nq * a.M + m) * a.LP + j1;
-                float2 pd = make_float2(0.f, 0.f);
-                if (key[t] >= 0) pd = dots[ul * LPA + j1];
-                const float gat = wa[t] * pd.x + wb[t] * pd.y;   // d out / d attention weight
-                const float gx = ga[t] * pd.x + gb[t] * pd.y;    // d out / d location
-                if (!FUSED) {
-                    if (on) {
-                        a.grad_attn[sidx] = gat;
-                        // dummy y (= 0.5 on an H = 1 level): BORDER clamps it, gradient exactly 0; ZEROS keeps the
-                        // row-0 weight 1 - |y*H - 0.5| whose slope the reference kernel reports (cuh:159)
-                        const float gy = a.pad_mode == MSDA_PAD_ZEROS ? -At[t] * gat : 0.f;
-                        *reinterpret_cast<float2 *>(a.grad_loc + 2 * sidx) = make_float2(gx, gy);
-                    }
-                } else {
-                    // softmax Jacobian: g_logit_s = A_s * (ga_s - sum_t A_t ga_t)
-                    const float dotsum = group_sum<LPA>(At[t] * gat);
-                    if (on) {
-                        a.grad_offs[sidx] = gx * dxd[t];
-                        a.grad_logits[sidx] = At[t] * (gat - dotsum);
-                    }
-                    if (a.grad_ref != nullptr) {
-                        float r0g = on ? gx : 0.f;   // d(loc)/d(ref0) = 1
-                        float r1g = 0.f;             // d(loc)/d(ref1) = off * 0.5 / P
-                        if (a.R == 2 && on) r1g = gx * raw[t].x * (0.5f * a.invP);
-                        if (p_pow2) {   // the P lanes of one level are contiguous and P-aligned
-                            for (int off = a.P >> 1; off >= 1; off >>= 1) {
-                                r0g += __shfl_xor_sync(kFull, r0g, off);
-                                r1g += __shfl_xor_sync(kFull, r1g, off);
-                            }
-                            if (on && (j1 & (a.P - 1)) == 0) {
-                                float *gp = a.grad_ref + (nq * a.L + lc.l) * a.R;
+                float gat[SPL], gx[SPL];
+                float part = 0.f;
+#pragma unroll
+                for (int s = 0; s < SPL; ++s) {
+                    float2 pd = make_float2(0.f, 0.f);
+                    if (key[t][s] >= 0) pd = dots[ul * LPT + s * LPA + j1];
+                    gat[s] = wa[t][s] * pd.x + wb[t][s] * pd.y;   // d out / d attention weight
+                    gx[s] = ga[t][s] * pd.x + gb[t][s] * pd.y;    // d out / d location
+                    part += At[t][s] * gat[s];
+                }
+                // softmax Jacobian: g_logit_s = A_s * (ga_s - sum_t A_t ga_t)
+                const float dotsum = FUSED ? group_sum<LPA>(part) : 0.f;
+#pragma unroll
+                for (int s = 0; s < SPL; ++s) {
+                    const bool on = lc[s].live && qv[t] >= 0;
+                    const int sidx = (nq * a.M + m) * a.LP + j1 + s * LPA;
+                    if (!FUSED) {
+                        if (on) {
+                            a.grad_attn[sidx] = gat[s];
+                            // dummy y (= 0.5 on an H = 1 level): BORDER clamps it, gradient exactly 0; ZEROS keeps the
+                            // row-0 weight 1 - |y*H - 0.5| whose slope the reference kernel reports (cuh:159)
+                            const float gy = a.pad_mode == MSDA_PAD_ZEROS ? -At[t][s] * gat[s] : 0.f;
+                            *reinterpret_cast<float2 *>(a.grad_loc + 2 * sidx) = make_float2(gx[s], gy);
+                        }
+                    } else {
+                        if (on) {
+                            a.grad_offs[sidx] = gx[s] * dxd[t][s];
+                            a.grad_logits[sidx] = At[t][s] * (gat[s] - dotsum);
+                        }
+                        if (a.grad_ref != nullptr) {
+                            float r0g = on ? gx[s] : 0.f;   // d(loc)/d(ref0) = 1
+                            float r1g = 0.f;                // d(loc)/d(ref1) = off * 0.5 / P
+                            if (a.R == 2 && on) r1g = gx[s] * raw[t][s].x * (0.5f * a.invP);
+                            if (p_pow2) {   // the P lanes of one level are contiguous and P-aligned
+                                for (int off = a.P >> 1; off >= 1; off >>= 1) {
+                                    r0g += __shfl_xor_sync(kFull, r0g, off);
+                                    r1g += __shfl_xor_sync(kFull, r1g, off);
+                                }
+                                if (on && (j1 & (a.P - 1)) == 0) {
+                                    float *gp = a.grad_ref + (nq * a.L + lc[s].l) * a.R;
+                                    atomicAdd(gp, r0g);
+                                    if (a.R == 2) atomicAdd(gp + 1, r1g);
+                                }
+                            } else if (on) {
+                                float *gp = a.grad_ref + (nq * a.L + lc[s].l) * a.R;
                                 atomicAdd(gp, r0g);
                                 if (a.R == 2) atomicAdd(gp + 1, r1g);
                             }
-                        } else if (on) {
-                            float *gp = a.grad_ref + (nq * a.L + lc.l) * a.R;
-                            atomicAdd(gp, r0g);
-                            if (a.R == 2) atomicAdd(gp + 1, r1g);
                         }
                     }
                 }

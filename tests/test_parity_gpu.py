@@ -186,6 +186,8 @@ def _nudge_off_knots(inp, P):
     dict(seed=23, N=1, M=4, D=32, T=cases.level_lengths(40), Lq=19, P=8, R=1),
     dict(seed=24, N=1, M=2, D=128, T=[30, 15], Lq=9, P=16, R=2),
     dict(seed=25, N=2, M=3, D=16, T=[12], Lq=5, P=3, R=1),
+    dict(seed=26, N=2, M=8, D=64, T=cases.level_lengths(120), Lq=70, P=16, R=2),   # L*P = 64, decoder tiling, boxes
+    dict(seed=27, N=1, M=4, D=64, T=cases.level_lengths(90), Lq=33, P=10, R=1),    # L*P = 40
 ])
 def test_fused_vs_oracle(dvc, cfg, pad, dtype):
     if dtype == torch.bfloat16 and cfg["D"] < 32:
@@ -356,6 +358,9 @@ def _encoder_inputs(seed, N, M, D, T0, P, jitter):
     dict(seed=31, N=2, M=8, D=64, T0=300, P=4, jitter=1.0),    # 10 time spans per (n, m): several tiles, halos
     dict(seed=32, N=1, M=4, D=64, T0=521, P=4, jitter=6.0),    # odd lengths, wide windows
     dict(seed=33, N=1, M=2, D=32, T0=160, P=8, jitter=40.0),   # windows that do not fit: L1 gather fallback
+    dict(seed=34, N=2, M=8, D=64, T0=300, P=16, jitter=2.0),   # L*P = 64: two samples per lane (lean kernels, SPL = 2)
+    dict(seed=35, N=1, M=4, D=64, T0=200, P=12, jitter=3.0),   # L*P = 48: SPL = 2 with dead lanes, P not a power of two
+    dict(seed=36, N=3, M=2, D=128, T0=97, P=9, jitter=1.5),    # L*P = 36, D = 128, odd everything
 ])
 def test_encoder_geometry_vs_oracle(dvc, cfg, pad, dtype):
     inp = _nudge_off_knots(_encoder_inputs(**cfg), cfg["P"])

@@ -53,6 +53,8 @@ CASES = [
     ("anet_dec", 2, 8, 64, cases.level_lengths(100), 10, 4, False, torch.float32),
     ("cap_m1_d512", 1, 1, 512, cases.level_lengths(200), 6, 4, False, torch.float32),
     ("p8_d32", 2, 4, 32, cases.level_lengths(64), 50, 8, False, torch.float32),
+    ("p16_l4", 2, 8, 64, cases.level_lengths(120), 37, 16, False, torch.float32),     # L*P = 64 (lean kernels, 2 samples/lane)
+    ("p12_l4", 1, 4, 64, cases.level_lengths(75), 21, 12, False, torch.float32),      # L*P = 48
     ("ref_test_2d_f64", 1, 2, 2, [(6, 4), (3, 2)], 2, 2, True, torch.float64),      # pdvc/ops/test.py:21-25
     ("ragged_2d", 2, 4, 16, [(5, 7), (3, 4), (1, 9)], 13, 3, True, torch.float32),
 ]
