@@ -511,6 +511,16 @@ __global__ void __launch_bounds__(kLeanThreads, MSDA_BWD_MINB) msda_bwd_lean_ker
         }
         if (j1 == 0 && ulv[t] < a.Q) uq[ulv[t]] = qv[t];
     }
+    __syncthreads();   // uq complete
+    // grad_out rows of the tile: issued while the raw inputs are still in flight, consumed after the sort
+    {
+        const unsigned char *gsrc = static_cast<const unsigned char *>(a.grad_out) + ((size_t)n * a.Lq * a.M + m) * rb;
+        constexpr int VPR = rb / 16;   // 16-byte vectors per row
+        for (int v = tid; v < Qc * VPR; v += kLeanThreads) {
+            const int ul = v / VPR, jj = v % VPR;
+            cp_async16(Gs + ul * rb + jj * 16, gsrc + (size_t)uq[ul] * a.M * rb + jj * 16);
+        }
+    }
 
     // ---- decode; per-level range of first rows ----
     int key[PASSES][SPL], rank[PASSES][SPL];
@@ -555,15 +565,6 @@ __global__ void __launch_bounds__(kLeanThreads, MSDA_BWD_MINB) msda_bwd_lean_ker
     __syncthreads();   // uq, win_lo / win_hi complete
     MSDA_PHASE_MARK
 
-    // grad_out rows of the tile (async; consumed after the sort)
-    {
-        const unsigned char *gsrc = static_cast<const unsigned char *>(a.grad_out) + ((size_t)n * a.Lq * a.M + m) * rb;
-        constexpr int VPR = rb / 16;   // 16-byte vectors per row
-        for (int v = tid; v < Qc * VPR; v += kLeanThreads) {
-            const int ul = v / VPR, jj = v % VPR;
-            cp_async16(Gs + ul * rb + jj * 16, gsrc + (size_t)uq[ul] * a.M * rb + jj * 16);
-        }
-    }
     // compact row index of slice row r at level l: wbase_l + r; tot = rows in all level windows (<= S)
     int tot = 0, my_base[SPL];
 #pragma unroll
