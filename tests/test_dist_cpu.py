@@ -96,3 +96,62 @@ def test_two_rank_ddp_training_keeps_replicas_identical():
     assert out[0][1] > 0 and out[1][1] > 0               # the step moved the parameters
     assert out[0][2] == 0.0 and out[1][2] == 0.0         # gradient all-reduce: replicas stay bit-identical
     assert all(l == l and abs(l) < 1e6 for l in out[0][0] + out[1][0])
+
+
+def _ddp_equiv_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    sys.path.insert(0, ROOT)
+    torch.set_num_threads(2)
+    from dense_video_captioning_b200.pdvc import PDVCConfig, Trainer, synthetic_video
+    _patch_cuda_modules_with_oracle()
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    cfg = PDVCConfig(feature_dim=64, num_queries=6, frame_embedding_num=32, vocab_size=40, transformer_ff_dim=128,
+                     enc_layers=1, dec_layers=2, transformer_dropout_prob=0.0, drop_prob=0.0)
+    tr = Trainer(cfg, "cpu", world_size=world, lr=1e-3)
+    losses = [float(tr.step(synthetic_video(cfg, n_gt=3, cap_len=5, seed=50 + 2 * step + rank))) for step in range(3)]
+    out[rank] = (losses, torch.cat([p.detach().flatten() for p in tr.params]).double().numpy())
+    dist.destroy_process_group()
+
+
+def test_two_rank_ddp_equals_one_process_at_equal_effective_batch():
+    """'1-GPU vs N-GPU loss curves on a fixed synthetic set agree at equal effective batch'.  Two ranks with one
+    video each per step (DDP averages the gradients) against one process that accumulates the gradients of the same two
+    videos and halves them: same losses, same parameters after three steps (up to fp32 summation order)."""
+    import numpy as np
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_ddp_equiv_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+
+    sys.path.insert(0, ROOT)
+    from dense_video_captioning_b200.ops.modules import MSDeformAttn, MSDeformAttnCap
+    from dense_video_captioning_b200.pdvc import PDVCConfig, Trainer, synthetic_video
+    from dense_video_captioning_b200.pdvc.train import to_device
+    saved = MSDeformAttn.forward, MSDeformAttnCap.forward
+    _patch_cuda_modules_with_oracle()
+    try:
+        cfg = PDVCConfig(feature_dim=64, num_queries=6, frame_embedding_num=32, vocab_size=40, transformer_ff_dim=128,
+                         enc_layers=1, dec_layers=2, transformer_dropout_prob=0.0, drop_prob=0.0)
+        tr = Trainer(cfg, "cpu", world_size=1, lr=1e-3)
+        single = []
+        for step in range(3):
+            tr.optimizer.zero_grad(set_to_none=True)
+            step_losses = []
+            for rank in range(world):
+                total, _, _ = tr.net(to_device(synthetic_video(cfg, n_gt=3, cap_len=5, seed=50 + 2 * step + rank), tr.device))
+                (total / world).backward()
+                step_losses.append(float(total))
+            torch.nn.utils.clip_grad_norm_(tr.params, tr.grad_clip)
+            tr.optimizer.step()
+            single.append(step_losses)
+        params = torch.cat([p.detach().flatten() for p in tr.params]).double().numpy()
+    finally:
+        MSDeformAttn.forward, MSDeformAttnCap.forward = saved
+    for step in range(3):
+        for rank in range(world):
+            assert abs(out[rank][0][step] - single[step][rank]) <= 2e-4 * abs(single[step][rank]), (step, rank)
+    assert np.abs(out[0][1] - out[1][1]).max() == 0.0
+    # Adam normalises the update, so tiny gradient differences are amplified where |grad| ~ eps: compare the bulk
+    diff = np.abs(out[0][1] - params)
+    assert np.quantile(diff, 0.999) <= 2e-4 and diff.max() <= 3 * 3e-3, (np.quantile(diff, 0.999), diff.max())
