@@ -127,7 +127,9 @@ class Trainer:
                 torch.cuda.current_stream().wait_stream(side)
             else:
                 self.net = DDP(self.net, gradient_as_bucket_view=True, broadcast_buffers=False)
-        self.optimizer = torch.optim.Adam(self.params, lr=lr, weight_decay=weight_decay)
+        # same update rule as the reference's torch.optim.Adam (train.py:100-104); on CUDA the single-kernel (fused) variant
+        self.optimizer = torch.optim.Adam(self.params, lr=lr, weight_decay=weight_decay,
+                                          fused=(self.device.type == "cuda"))
         self.grad_clip = grad_clip
         self.weight_dict = self.criterion.weight_dict
 
