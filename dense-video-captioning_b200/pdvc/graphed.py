@@ -26,6 +26,7 @@ from torch import nn
 
 from .model import caption_steps
 
+
 def pyramid_lengths(t0, n_levels):
     """Level lengths of the feature pyramid: Conv1d(k3,s2,p1) per extra level (pdvc/base_encoder.py:37-41)."""
     out = [int(t0)]
@@ -40,7 +41,6 @@ def graph_module(module, sample_args, warmup=3, autocast=None):
     trainable parameters (the scheme of torch.cuda.make_graphed_callables, written out so that the capture runs in
     `thread_local` error mode -- NCCL's watchdog thread may poll events while a rank is capturing -- and outputs that
     carry no gradient are marked non-differentiable)."""
-    import contextlib
     params = tuple(p for p in module.parameters() if p.requires_grad)
     surface = tuple(sample_args) + params
     diff_inputs = tuple(t for t in surface if t.requires_grad)
@@ -218,12 +218,13 @@ class LossStage(nn.Module):
 class StagedStep(nn.Module):
     """forward(dt) -> (total loss, dict of loss terms) for ONE video, as stage 1 -> host matching -> stage 2."""
 
-    def __init__(self, model, criterion, graphs=True, amp=False):
+    def __init__(self, model, criterion, graphs=True, amp=False, max_graphs=64):
         super().__init__()
         self.model = model
         self.criterion = criterion
         self.graphs = graphs
         self.amp = amp
+        self.max_graphs = max_graphs      # stage-2 graphs kept (one per shape key, least recently used dropped first)
         self.stage1 = FeatureStage(model, criterion.matcher)
         self.__dict__["_stage1_call"] = None
         self.__dict__["_stage2"] = {}
@@ -289,7 +290,11 @@ class StagedStep(nn.Module):
             if use_graphs:
                 sample = tuple(a.detach().clone().requires_grad_(a.requires_grad) for a in args2)
                 stage2 = self._graph(stage2, sample)
+            if len(self._stage2) >= self.max_graphs:
+                self._stage2.pop(next(iter(self._stage2)))
             self._stage2[key] = stage2
+        else:
+            self._stage2[key] = self._stage2.pop(key)       # most recently used last
         total, terms = self._stage2[key](*args2)
         names = [name + ('' if lid == n_pred - 1 else f'_{lid}') for lid in range(n_pred) for name in LOSS_TERMS]
         return total, dict(zip(names, terms.unbind(0))), (q_host, t_host)
