@@ -226,7 +226,7 @@ class StagedStep(nn.Module):
         self.amp = amp
         self.max_graphs = max_graphs      # stage-2 graphs kept (one per shape key, least recently used dropped first)
         self.stage1 = FeatureStage(model, criterion.matcher)
-        self.__dict__["_stage1_call"] = None
+        self.__dict__["_stage1"] = {}
         self.__dict__["_stage2"] = {}
         self.__dict__["_staging"] = {}
 
@@ -263,6 +263,16 @@ class StagedStep(nn.Module):
     def _graph(self, module, args):
         return graph_module(module, args, autocast=torch.bfloat16 if self.amp else None)
 
+    def _cached(self, cache, key, make):
+        """Least-recently-used cache of captured stages, at most max_graphs per stage."""
+        if key in cache:
+            cache[key] = cache.pop(key)                     # most recently used last
+        else:
+            if len(cache) >= self.max_graphs:
+                cache.pop(next(iter(cache)))
+            cache[key] = make()
+        return cache[key]
+
     # ---- the step --------------------------------------------------------------------------------------------
     def forward(self, dt):
         vf, valid, duration = dt['video_tensor'], dt['video_mask'], dt['video_length'][:, 1]
@@ -270,9 +280,10 @@ class StagedStep(nn.Module):
         target = dt['video_target'][0]
         args1 = (vf, valid, duration, target['boxes'], target['labels'])
         use_graphs = self.graphs and vf.is_cuda
-        if use_graphs and self._stage1_call is None:
-            self._stage1_call = self._graph(self.stage1, tuple(a.detach().clone() for a in args1))
-        stage1 = self._stage1_call if use_graphs else self.stage1
+        stage1 = self.stage1
+        if use_graphs:      # the matching costs are part of stage 1, so its graph depends on the event count too
+            key1 = (int(vf.shape[1]), int(target['boxes'].shape[0]))
+            stage1 = self._cached(self._stage1, key1, lambda: self._graph(self.stage1, tuple(a.detach().clone() for a in args1)))
         hs, init_ref, inter_refs, logits, counts, boxes, memory, mask_flat, valid_ratios, costs = stage1(*args1)
         n_pred = hs.shape[0]
         num_boxes = self._num_boxes(int(target['boxes'].shape[0]), vf.device)
@@ -284,17 +295,15 @@ class StagedStep(nn.Module):
         args2 = (hs, init_ref, inter_refs.detach(), logits, counts, boxes, memory, mask_flat, valid_ratios.detach(),
                  target['boxes'], target['labels'], dt['cap_tensor'], dt['cap_mask'], num_boxes, q_idx, t_idx)
         key = (int(target['boxes'].shape[0]), q_host.shape[1], n_steps, int(vf.shape[1]), int(dt['cap_tensor'].shape[1]))
-        if key not in self._stage2:
+
+        def make_stage2():
             lengths = pyramid_lengths(vf.shape[1], self.model.cfg.num_feature_levels)
             stage2 = LossStage(self.model, self.criterion, n_steps, lengths)
             if use_graphs:
                 sample = tuple(a.detach().clone().requires_grad_(a.requires_grad) for a in args2)
                 stage2 = self._graph(stage2, sample)
-            if len(self._stage2) >= self.max_graphs:
-                self._stage2.pop(next(iter(self._stage2)))
-            self._stage2[key] = stage2
-        else:
-            self._stage2[key] = self._stage2.pop(key)       # most recently used last
-        total, terms = self._stage2[key](*args2)
+            return stage2
+
+        total, terms = self._cached(self._stage2, key, make_stage2)(*args2)
         names = [name + ('' if lid == n_pred - 1 else f'_{lid}') for lid in range(n_pred) for name in LOSS_TERMS]
         return total, dict(zip(names, terms.unbind(0))), (q_host, t_host)

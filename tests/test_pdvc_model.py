@@ -199,3 +199,20 @@ def test_trainer_steps_and_loss_decreases(mode):
     losses = [float(tr.step(video)) for _ in range(12)]
     assert all(np.isfinite(losses)), losses
     assert losses[-1] < losses[0], losses
+
+
+@pytest.mark.gpu
+def test_graph_trainer_tracks_eager_trainer_over_changing_shapes():
+    """Videos with different event counts and caption lengths: every new (events, pairs, word steps) key captures its
+    own stage-2 graph, earlier keys are replayed later; the loss trajectory follows the eager ('staged') trainer."""
+    from dense_video_captioning_b200.pdvc import Trainer, synthetic_video
+    plan = [(2, 4), (5, 7), (3, 4), (5, 7), (2, 4), (3, 6), (5, 7), (2, 4)]
+    runs = {}
+    for mode in ("staged", "graphs"):
+        tr = Trainer("anet_c3d_pdvc", "cuda:0", dropout=0.0, lr=2e-5, mode=mode, seed=3)
+        runs[mode] = [float(tr.step(synthetic_video(tr.cfg, n_gt, cap_len, seed=100 + i)))
+                      for i, (n_gt, cap_len) in enumerate(plan)]
+        if mode == "graphs":
+            assert len(tr.net._stage2) == 4            # (2,4) (5,7) (3,4) (3,6)
+    for a, b in zip(runs["staged"], runs["graphs"]):
+        assert np.isfinite(b) and abs(a - b) <= 2e-3 * abs(a), (runs["staged"], runs["graphs"])

@@ -47,7 +47,7 @@ for par in (False, True):
             g.replay()
         b.record(); torch.cuda.synchronize()
         return a.elapsed_time(b) / 10
-    s1 = tr.net._stage1_call.graphs
+    s1 = next(iter(tr.net._stage1.values())).graphs
     s2 = next(iter(tr.net._stage2.values())).graphs
     print(f"parallel_layers={par}: forward-graph replays: stage1 {replay_ms(s1[0]):.2f} ms | stage2 {replay_ms(s2[0]):.2f} ms")
     print(f"parallel_layers={par}: forward (stage1 + match + stage2) {sorted(fw)[5]:.2f} ms, backward {sorted(bw)[5]:.2f} ms")
