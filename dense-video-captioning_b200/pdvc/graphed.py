@@ -147,6 +147,7 @@ class LossStage(nn.Module):
         self.n_steps = tuple(n_steps)
         self.level_lengths = list(level_lengths)
         self.parallel_layers = True
+        self.batch_layers = True
         self.__dict__["_streams"] = []
 
     def _side_streams(self, n, device):
@@ -154,17 +155,9 @@ class LossStage(nn.Module):
             self._streams.append(torch.cuda.Stream(device))
         return self._streams[:n]
 
-    def forward(self, hs, init_reference, inter_references, logits, counts, boxes, memory, mask_flat, valid_ratios,
-                tgt_boxes, tgt_labels, cap_tensor, cap_mask, num_boxes, q_idx, t_idx):
-        model, crit = self._model, self._criterion
+    def _caption_losses_per_layer(self, hs, init_reference, inter_references, others, cap_tensor, cap_mask, q_idx, t_idx):
+        """Caption heads that differ per layer (share_caption_head=0) or layers with different word-step counts."""
         n_pred = hs.shape[0]
-        shapes, starts = model.transformer.level_tensors(self.level_lengths, hs.device)
-        others = {'memory': memory, 'mask_flatten': mask_flat, 'spatial_shapes': shapes, 'level_start_index': starts,
-                  'valid_ratios': valid_ratios, 'level_lengths': self.level_lengths}
-        targets = [{'boxes': tgt_boxes, 'labels': tgt_labels}]
-        pairs = q_idx.shape[1]
-        batch = torch.zeros(pairs, dtype=torch.long, device=hs.device)
-
         # The caption loops of the decoder layers are independent chains of ~1 300 tiny kernels each: on the GPU every
         # layer's loop runs on its own stream (inside a capture these become parallel branches of the graph, forward and --
         # because autograd replays each node on the stream it ran on -- backward).  cuDNN's RNN calls serialise across
@@ -195,6 +188,53 @@ class LossStage(nn.Module):
             with on_stream(lid):
                 c = t_idx[lid]
                 cap.append(self.caption_head[lid].build_loss(decoders[lid].result(), cap_tensor[:, 1:][c], cap_mask[:, 1:][c]).mean())
+        return cap, side, main
+
+    def forward(self, hs, init_reference, inter_references, logits, counts, boxes, memory, mask_flat, valid_ratios,
+                tgt_boxes, tgt_labels, cap_tensor, cap_mask, num_boxes, q_idx, t_idx):
+        model, crit = self._model, self._criterion
+        n_pred = hs.shape[0]
+        shapes, starts = model.transformer.level_tensors(self.level_lengths, hs.device)
+        others = {'memory': memory, 'mask_flatten': mask_flat, 'spatial_shapes': shapes, 'level_start_index': starts,
+                  'valid_ratios': valid_ratios, 'level_lengths': self.level_lengths}
+        targets = [{'boxes': tgt_boxes, 'labels': tgt_labels}]
+        pairs = q_idx.shape[1]
+        batch = torch.zeros(pairs, dtype=torch.long, device=hs.device)
+
+        shared = (self.batch_layers and len(set(self.n_steps)) == 1 and n_pred > 1
+                  and all(head is self.caption_head[0] for head in self.caption_head)
+                  and self.caption_head[0].core.n_levels == len(self.level_lengths))
+        if shared:
+            # One caption head shared by all decoder layers (opts.py:148, the default): the layers' matched pairs are
+            # independent sentences for the SAME weights, so they are decoded as ONE batch of n_pred * pairs sentences --
+            # one chain of word steps instead of n_pred.  Layer 0's single-coordinate reference (pdvc.py:262) is written in
+            # the two-coordinate form with width 2P/T_l, for which the sampler's `ref0 + off/P * ref1 * 0.5`
+            # (ms_deform_attn_for_caption.py:107-109) is the `ref0 + off/T_l` of :104-106.
+            head = self.caption_head[0]
+            side = self._side_streams(1, hs.device) if hs.is_cuda else []
+            main = torch.cuda.current_stream() if side else None
+            for s_ in side:
+                s_.wait_stream(main)
+            with (torch.cuda.stream(side[0]) if side else contextlib.nullcontext()):
+                layer = torch.arange(n_pred, device=hs.device)[:, None]
+                hs_pairs = hs[:, 0][layer, q_idx].reshape(1, n_pred * pairs, -1)
+                valid = valid_ratios[0]                                                     # (L,)
+                first = init_reference[0, q_idx[0]] * valid[None, :]                        # (pairs, L)
+                width = (2.0 * head.core.n_points) / shapes.to(first.dtype)
+                refs = [torch.stack([first, width[None, :].expand_as(first)], -1)]
+                if n_pred > 1:
+                    later = inter_references[:n_pred - 1, 0][layer[:-1], q_idx[1:]]          # (n_pred-1, pairs, 2)
+                    refs.append((later[:, :, None, :] * valid[None, None, :, None]).reshape(-1, valid.shape[0], 2))
+                ref = torch.cat(refs, 0)[None]                                              # (1, n_pred*pairs, L, 2)
+                flat = t_idx.reshape(-1)
+                decoder = head.begin(hs_pairs, ref, memory, shapes, starts, mask_flat, cap_tensor[flat].long())
+                for i in range(self.n_steps[0]):
+                    decoder.step(i)
+                per_sentence = head.build_loss(decoder.result(), cap_tensor[:, 1:][flat], cap_mask[:, 1:][flat])
+                cap = list(per_sentence.view(n_pred, pairs).mean(1).unbind(0))
+        else:
+            cap, side, main = self._caption_losses_per_layer(hs, init_reference, inter_references, others, cap_tensor,
+                                                             cap_mask, q_idx, t_idx)
         set_losses = []
         for lid in range(n_pred):
             out = {'pred_logits': logits[lid], 'pred_count': counts[lid], 'pred_boxes': boxes[lid]}
