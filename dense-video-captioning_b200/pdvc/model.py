@@ -22,6 +22,7 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
+from ..ops.functions import get_default_padding_mode
 from ..ops.modules import MSDeformAttnCap
 from .transformer import DeformableTransformer, inverse_sigmoid
 
@@ -176,10 +177,17 @@ class ShowAttendTellCore(nn.Module):
         k = self.n_levels * self.n_points
         joint_query = torch.cat((state[0][-1].unsqueeze(0), query), 2)
         clip = self.deformable_att(joint_query, reference_points, memory, temporal_shapes, level_start_index,
-                                   padding_mask, projected_value=projected_value)       # (N*M, D, Lq, L, P)
-        clip = clip.reshape(n, self.n_heads, -1, lq, k).permute(0, 3, 1, 4, 2)            # (N, Lq, M, L*P, D)
-        clip = clip.reshape(n * lq, self.n_heads, k, self.att_feat_size)
-        scores = self.ctx2att(clip) + self.h2att(state[0][-1])[:, None, None, :]
+                                   padding_mask, projected_value=projected_value)       # (N*M, D', Lq, L, P)
+        clip = clip.reshape(n, self.n_heads, -1, lq, k).permute(0, 3, 1, 4, 2)            # (N, Lq, M, L*P, D')
+        clip = clip.reshape(n * lq, self.n_heads, k, -1)
+        if clip.shape[-1] == self.att_feat_size + self.att_hid_size:
+            # `projected_value` carried ctx2att(value) next to value (SentenceDecoder): interpolation weights sum to 1 in
+            # border mode, so sampling the projected rows IS ctx2att of the sampled rows (LSTM_DSA.py:247) without the
+            # per-word GEMM, its two backward GEMMs and the per-word weight-gradient accumulation
+            clip, ctx = clip[..., :self.att_feat_size], clip[..., self.att_feat_size:]
+        else:
+            ctx = self.ctx2att(clip)
+        scores = ctx + self.h2att(state[0][-1])[:, None, None, :]
         scores = self.alpha_net(torch.tanh(scores)).view(-1, k)
         weight = F.softmax(scores, dim=1)
         attended = torch.bmm(weight.unsqueeze(1), clip.reshape(-1, k, self.att_feat_size)).squeeze(1)
@@ -262,17 +270,25 @@ class SentenceDecoder:
             head, hs, ref, memory, shapes, starts, mask, seq)
         pairs = hs.shape[1]
         self.state = (hs.new_zeros(head.num_layers, pairs, head.rnn_size), hs.new_zeros(head.num_layers, pairs, head.rnn_size))
-        self.value = head.core.deformable_att.project_value(memory, mask).contiguous()   # once per sentence, not per word
+        core = head.core
+        value = core.deformable_att.project_value(memory, mask)                           # once per sentence, not per word
+        if value.is_cuda and core.att_hid_size > 0 and (core.deformable_att.padding_mode or get_default_padding_mode()) == "border":
+            value = torch.cat((value, core.ctx2att(value)), -1)                           # see ShowAttendTellCore.forward
+        self.value = value.contiguous()
+        self.embedded = head.embed(seq)                     # teacher forcing: every input word is known up front
         self.outputs = []
 
     def step(self, i):
         head = self.head
-        out, self.state = head.core(head.embed(self.seq[:, i]), self.state, self.hs, self.ref, self.memory, self.shapes,
+        out, self.state = head.core(self.embedded[:, i], self.state, self.hs, self.ref, self.memory, self.shapes,
                                     self.starts, self.mask, projected_value=self.value)
-        self.outputs.append(F.log_softmax(head.logit(head.dropout(out)), dim=1))
+        self.outputs.append(out)
 
     def result(self):
-        return torch.stack(self.outputs, 1)
+        """Log-probabilities (pairs, steps, vocab+1).  Under teacher forcing the vocabulary projection never feeds the
+        recurrence, so LSTM_DSA.py:95-96 (dropout, logit, log_softmax per word) runs once over all word steps."""
+        head = self.head
+        return F.log_softmax(head.logit(head.dropout(torch.stack(self.outputs, 1))), dim=2)
 
 
 def caption_steps(seq_host):
