@@ -35,6 +35,7 @@ SIGNATURES = {
     "msda_sample_backward": (_i, [_vp] * 7 + [_vp, _sz] + [_i] * 7 + [_i, _i, _u, _vp]),
     "msda_cap_sample_forward": (_i, [_vp] * 6 + [_i] * 8 + [_i, _i, _u, _vp]),
     "msda_cap_sample_backward": (_i, [_vp] * 9 + [_vp, _sz] + [_i] * 8 + [_i, _i, _u, _vp]),
+    "msda_skinny_linear_f32": (_i, [_vp] * 4 + [_i] * 3 + [_vp]),
 }
 
 _lib = None

@@ -13,6 +13,7 @@
 #include "msda_tile.cuh"
 #include "msda_lean.cuh"
 #include "msda_capsample.cuh"
+#include "msda_steplinear.cuh"
 
 using namespace msda;
 
@@ -708,6 +709,18 @@ int msda_cap_sample_forward(const void *value, const int64_t *temporal_shapes, c
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (dtype == MSDA_F32) msda_cap_fwd_kernel<float><<<(int)blocks, 256, 0, st>>>(a);
     else msda_cap_fwd_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, st>>>(a);
+    return check_launch();
+}
+
+int msda_skinny_linear_f32(const float *x, const float *weight, const float *bias, float *y, int M, int N, int K,
+                           void *stream)
+{
+    g_launches = 0;
+    if (M <= 0 || N <= 0 || K <= 0 || (K & 3)) return MSDA_ERR_SHAPE;
+    if (!x || !weight || !y) return MSDA_ERR_NULL;
+    if (!aligned16(x) || !aligned16(weight)) return MSDA_ERR_ALIGN;
+    const dim3 grid((N + kSkinnyWarps * kSkinnyNW - 1) / (kSkinnyWarps * kSkinnyNW), (M + kSkinnyRows - 1) / kSkinnyRows);
+    msda_skinny_linear_kernel<<<grid, kSkinnyWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(x, weight, bias, y, M, N, K);
     return check_launch();
 }
 

@@ -397,3 +397,83 @@ def ms_deform_attn_core_pytorch(value, value_spatial_shapes, sampling_locations,
     if return_value:
         return MSDeformSampleFunction.apply(value, shapes2, lsi, loc)
     return MSDeformAttnFunction.apply(value, shapes2, lsi, loc, attention_weights.contiguous(), 64)
+
+
+def skinny_linear(x, weight, bias=None):
+    """y = x @ weight.T (+ bias) for an input with few rows: x (M,K), weight (N,K) fp32 CUDA tensors, K % 4 == 0
+    (csrc/msda_steplinear.cuh; C ABI msda_skinny_linear_f32)."""
+    _check_cuda_contig(x=x, weight=weight)
+    _require(x.dtype == torch.float32 and weight.dtype == torch.float32, "skinny_linear takes float32 tensors")
+    _require(x.dim() == 2 and weight.dim() == 2 and x.shape[1] == weight.shape[1], "x (M,K) and weight (N,K) expected")
+    _require(x.shape[1] % 4 == 0, "K must be a multiple of 4")
+    if bias is not None:
+        _check_cuda_contig(bias=bias)
+        _require(bias.dtype == torch.float32 and bias.numel() == weight.shape[0], "bias must be (N,) float32")
+    M, K = x.shape
+    N = weight.shape[0]
+    y = torch.empty((M, N), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        rc = _lib.lib().msda_skinny_linear_f32(_ptr(x), _ptr(weight), _ptr(bias), _ptr(y), M, N, K, _stream(x.device))
+    _lib.check(rc, "msda_skinny_linear_f32")
+    return y
+
+
+class StepLinear:
+    """One nn.Linear applied once per word step of a teacher-forced decoding run (`sampling_offsets` of MSDeformAttnCap,
+    ms_deform_attn_for_caption.py:100; `h2att`, LSTM_DSA.py:249), for ONE forward/backward pass:
+
+      * forward and data gradient through the few-row kernel (skinny_linear), fp32 also under autocast;
+      * the weight and bias gradients of all steps in ONE GEMM / ONE reduction: each step's backward only records its
+        (input, grad_output); step 0 -- whose backward runs last, every later step depends on it through the LSTM state --
+        computes  dW = [dY_0; ...; dY_n]^T [X_0; ...; X_n]  instead of n GEMMs and 2n gradient accumulations.
+
+    Steps must be applied in order 0, 1, 2, ... and each exactly once per pass (checked when the gradients are formed)."""
+
+    def __init__(self, linear):
+        self.weight, self.bias = linear.weight, linear.bias
+        self.calls = 0
+        self._pending = []
+        self._weight_t = None
+
+    def __call__(self, x):
+        index, self.calls = self.calls, self.calls + 1
+        return _StepLinearFunction.apply(x, self.weight, self.bias, self, index)
+
+    def _transposed(self, weight):
+        if self._weight_t is None:
+            self._weight_t = weight.t().contiguous()          # once per backward pass, shared by all steps
+        return self._weight_t
+
+
+class _StepLinearFunction(Function):
+    @staticmethod
+    @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    def forward(ctx, x, weight, bias, owner, index):
+        lead = x.shape[:-1]
+        x2 = x.reshape(-1, x.shape[-1]).contiguous()
+        ctx.save_for_backward(x2, weight)
+        ctx.owner, ctx.index, ctx.lead, ctx.has_bias = owner, index, lead, bias is not None
+        return skinny_linear(x2, weight.contiguous(), bias).view(*lead, weight.shape[0])
+
+    @staticmethod
+    @once_differentiable
+    @torch.amp.custom_bwd(device_type="cuda")
+    def backward(ctx, grad_y):
+        x2, weight = ctx.saved_tensors
+        owner = ctx.owner
+        g2 = grad_y.reshape(-1, grad_y.shape[-1]).contiguous().float()
+        grad_x = None
+        if ctx.needs_input_grad[0]:
+            grad_x = skinny_linear(g2, owner._transposed(weight), None).view(*ctx.lead, weight.shape[1])
+        owner._pending.append((ctx.index, x2, g2))
+        if ctx.index != 0:
+            return grad_x, None, None, None, None
+        pending, owner._pending, owner._weight_t = owner._pending, [], None
+        _require(sorted(i for i, _, _ in pending) == list(range(owner.calls)),
+                 "StepLinear: every step must take part in the backward pass exactly once")
+        owner.calls = 0
+        xs = torch.cat([x for _, x, _ in pending])
+        gs = torch.cat([g for _, _, g in pending])
+        grad_w = gs.t().mm(xs) if ctx.needs_input_grad[1] else None
+        grad_b = gs.sum(0) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        return grad_x, grad_w, grad_b, None, None

@@ -90,8 +90,9 @@ class _MSDeformFrontEnd(nn.Module):
         return value.view(N, Len_in, self.n_heads, self.d_model // self.n_heads)
 
     def _project(self, query, reference_points, input_flatten, input_spatial_shapes, input_padding_mask,
-                 projected_value=None, need_logits=True):
-        """value (N,S,M,D), raw offsets and logits (N,Lq,M,L,P) -- ms_deform_attn.py:95-100."""
+                 projected_value=None, need_logits=True, sampling_offsets=None):
+        """value (N,S,M,D), raw offsets and logits (N,Lq,M,L,P) -- ms_deform_attn.py:95-100.  `sampling_offsets`: the
+        output of self.sampling_offsets(query) when the caller has already computed it (functions.StepLinear)."""
         if not query.is_cuda:
             raise RuntimeError("MSDeformAttn (B200 build) runs on CUDA tensors only: there is no CPU path "
                                "(the reference falls back to F.grid_sample here, ms_deform_attn.py:123-124)")
@@ -102,7 +103,9 @@ class _MSDeformFrontEnd(nn.Module):
             raise ValueError('Last dim of reference_points must be 1 or 2, but get {} instead.'.format(
                 reference_points.shape[-1]))
         value = projected_value if projected_value is not None else self.project_value(input_flatten, input_padding_mask)
-        offsets = self.sampling_offsets(query).view(N, Len_q, self.n_heads, self.n_levels, self.n_points)
+        if sampling_offsets is None:
+            sampling_offsets = self.sampling_offsets(query)
+        offsets = sampling_offsets.view(N, Len_q, self.n_heads, self.n_levels, self.n_points)
         logits = None
         if need_logits:
             logits = self.attention_weights(query).view(N, Len_q, self.n_heads, self.n_levels, self.n_points)

@@ -16,9 +16,10 @@ class MSDeformAttnCap(_MSDeformFrontEnd):
         super().__init__(d_model, n_levels, n_heads, n_points)
 
     def forward(self, query, reference_points, input_flatten, input_spatial_shapes, input_level_start_index,
-                input_padding_mask=None, projected_value=None):
+                input_padding_mask=None, projected_value=None, sampling_offsets=None):
         value, offsets, logits = self._project(query, reference_points, input_flatten, input_spatial_shapes,
-                                               input_padding_mask, projected_value, need_logits=False)
+                                               input_padding_mask, projected_value, need_logits=False,
+                                               sampling_offsets=sampling_offsets)
         value = value.contiguous()
         if MSDeformCapSampleFunction.supported(value):
             # one fused kernel each way (csrc/msda_capsample.cuh); the reference's (N*M, D, Lq, L, P) is returned as a

@@ -22,9 +22,12 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
-from ..ops.functions import get_default_padding_mode
+from ..ops.functions import StepLinear, get_default_padding_mode
 from ..ops.modules import MSDeformAttnCap
 from .transformer import DeformableTransformer, inverse_sigmoid
+
+
+USE_STEP_LINEAR = True     # few-row kernels + deferred weight gradients for the Linear layers on the caption recurrence
 
 
 @dataclass
@@ -172,12 +175,17 @@ class ShowAttendTellCore(nn.Module):
             self.alpha_net = nn.Linear(self.att_hid_size, 1)
 
     def forward(self, xt, state, query, reference_points, memory, temporal_shapes, level_start_index, padding_mask,
-                projected_value=None):
+                projected_value=None, step_linears=None):
+        """`step_linears`: {'h2att', 'sampling_offsets'} -> functions.StepLinear standing in for the two Linear layers on
+        the recurrence (same weights; SentenceDecoder makes them per decoding run)."""
         n, lq = reference_points.shape[:2]
         k = self.n_levels * self.n_points
         joint_query = torch.cat((state[0][-1].unsqueeze(0), query), 2)
+        extra = {}
+        if step_linears is not None:
+            extra["sampling_offsets"] = step_linears["sampling_offsets"](joint_query)
         clip = self.deformable_att(joint_query, reference_points, memory, temporal_shapes, level_start_index,
-                                   padding_mask, projected_value=projected_value)       # (N*M, D', Lq, L, P)
+                                   padding_mask, projected_value=projected_value, **extra)   # (N*M, D', Lq, L, P)
         clip = clip.reshape(n, self.n_heads, -1, lq, k).permute(0, 3, 1, 4, 2)            # (N, Lq, M, L*P, D')
         clip = clip.reshape(n * lq, self.n_heads, k, -1)
         if clip.shape[-1] == self.att_feat_size + self.att_hid_size:
@@ -187,7 +195,8 @@ class ShowAttendTellCore(nn.Module):
             clip, ctx = clip[..., :self.att_feat_size], clip[..., self.att_feat_size:]
         else:
             ctx = self.ctx2att(clip)
-        scores = ctx + self.h2att(state[0][-1])[:, None, None, :]
+        h2att = step_linears["h2att"] if step_linears is not None else self.h2att
+        scores = ctx + h2att(state[0][-1])[:, None, None, :]
         scores = self.alpha_net(torch.tanh(scores)).view(-1, k)
         weight = F.softmax(scores, dim=1)
         attended = torch.bmm(weight.unsqueeze(1), clip.reshape(-1, k, self.att_feat_size)).squeeze(1)
@@ -276,12 +285,16 @@ class SentenceDecoder:
             value = torch.cat((value, core.ctx2att(value)), -1)                           # see ShowAttendTellCore.forward
         self.value = value.contiguous()
         self.embedded = head.embed(seq)                     # teacher forcing: every input word is known up front
+        self.step_linears = None
+        if USE_STEP_LINEAR and value.is_cuda and core.att_hid_size > 0 and core.h2att.weight.dtype == torch.float32:
+            self.step_linears = {"h2att": StepLinear(core.h2att),
+                                 "sampling_offsets": StepLinear(core.deformable_att.sampling_offsets)}
         self.outputs = []
 
     def step(self, i):
         head = self.head
         out, self.state = head.core(self.embedded[:, i], self.state, self.hs, self.ref, self.memory, self.shapes,
-                                    self.starts, self.mask, projected_value=self.value)
+                                    self.starts, self.mask, projected_value=self.value, step_linears=self.step_linears)
         self.outputs.append(out)
 
     def result(self):

@@ -186,6 +186,16 @@ int msda_cap_sample_backward(const void *value, const int64_t *temporal_shapes,
                              int N, int S, int M, int D, int L, int Lq, int P, int R, int dtype,
                              int pad_mode, unsigned flags, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Linear layer with a few input rows (the caption head's per-word projections):
+ *   y[m,n] = sum_k x[m,k] * weight[n,k] (+ bias[n]);  x (M,K), weight (N,K), y (M,N), all f32,
+ *   K % 4 == 0, x and weight 16-byte aligned, bias NULL to skip.  Replaces, for the word loop,
+ *   nn.Linear `sampling_offsets` (pdvc/ops/modules/ms_deform_attn_for_caption.py:100) and `h2att`
+ *   (pdvc/CaptioningHead/LSTM_DSA.py:249); the data gradient is the same call on the transposed weight.
+ * ------------------------------------------------------------------------------------------- */
+int msda_skinny_linear_f32(const float *x, const float *weight, const float *bias, float *y, int M,
+                           int N, int K, void *stream);
+
 /* Number of kernels the last call on this thread launched (bench.py's gpu_launches). */
 int msda_last_launch_count(void);
 

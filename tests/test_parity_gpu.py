@@ -530,3 +530,48 @@ def test_caption_module_returns_reference_shape_as_view(dvc):
     assert tuple(out.shape) == (1, 512, 6, 4, 4)
     back = out.reshape(1, 1, 512, 6, 16).permute(0, 3, 1, 4, 2)
     assert back.is_contiguous()
+
+
+@pytest.mark.parametrize("M,N,K", [(12, 512, 512), (12, 16, 1024), (1, 7, 4), (9, 33, 516), (30, 1608, 512), (17, 2048, 1536)])
+def test_skinny_linear_matches_torch_fp32(M, N, K):
+    """Floating-point kernel: compared with F.linear in float64 at fp32 rounding level (rel 2e-6 of the row scale)."""
+    from dense_video_captioning_b200.ops.functions import skinny_linear
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(M, K, generator=g).cuda()
+    w = torch.randn(N, K, generator=g).cuda()
+    b = torch.randn(N, generator=g).cuda()
+    want = torch.nn.functional.linear(x.double(), w.double(), b.double())
+    got = skinny_linear(x, w, b)
+    scale = float((x.double().abs() @ w.double().abs().t()).max())
+    assert float((got.double() - want).abs().max()) <= 2e-6 * scale
+    got = skinny_linear(x, w)
+    assert float((got.double() - (want - b.double())).abs().max()) <= 2e-6 * scale
+
+
+def test_step_linear_gradients_match_linear_in_a_recurrence():
+    """StepLinear inside a recurrence (each step's input depends on the previous step's output): outputs, input
+    gradients and the deferred weight / bias gradients equal nn.Linear's."""
+    from dense_video_captioning_b200.ops.functions import StepLinear
+    torch.manual_seed(2)
+    lin = torch.nn.Linear(64, 64).cuda()
+    x0 = torch.randn(10, 64, device="cuda", requires_grad=True)
+    drive = torch.randn(7, 10, 64, device="cuda")
+
+    def run(apply):
+        h, outs = x0, []
+        for i in range(7):
+            h = torch.tanh(apply(h) + drive[i])
+            outs.append(h)
+        loss = (torch.stack(outs) ** 2).sum()
+        grads = torch.autograd.grad(loss, [x0, lin.weight, lin.bias])
+        return [loss.detach()] + list(grads)
+
+    want = run(lin)
+    step = StepLinear(lin)
+    got = run(step)
+    assert step.calls == 0 and not step._pending          # the pass was closed by step 0's backward
+    for a, b in zip(got, want):
+        assert float((a - b).abs().max()) <= 2e-5 * float(b.abs().max())
+    got2 = run(step)                                         # reusable after a complete pass
+    for a, b in zip(got2, want):
+        assert float((a - b).abs().max()) <= 2e-5 * float(b.abs().max())

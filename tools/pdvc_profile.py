@@ -25,6 +25,28 @@ def graph_mode_profile(tr):
         float(tr.step(video))
     torch.cuda.synchronize()
     print(f"{tr.mode}: {(time.perf_counter() - t0) / 20 * 1e3:.2f} ms/step")
+    # device time of each graph replay, in issue order (stage 1 fwd, stage 2 fwd, stage 2 bwd, stage 1 bwd)
+    marks, replay = [], torch.cuda.CUDAGraph.replay
+
+    def timed_replay(self):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        replay(self)
+        b.record()
+        marks.append((a, b))
+
+    torch.cuda.CUDAGraph.replay = timed_replay
+    try:
+        first = torch.cuda.Event(enable_timing=True)
+        last = torch.cuda.Event(enable_timing=True)
+        first.record()
+        float(tr.step(video))
+        last.record()
+        torch.cuda.synchronize()
+    finally:
+        torch.cuda.CUDAGraph.replay = replay
+    print("graph replays (device ms, issue order):", " ".join(f"{a.elapsed_time(b):.2f}" for a, b in marks),
+          f"| whole step {first.elapsed_time(last):.2f}")
     with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
         for _ in range(3):
             float(tr.step(video))
@@ -36,6 +58,19 @@ def graph_mode_profile(tr):
     print(f"kernel nodes per step: {n_launch:.0f}, summed device time {dev_ms:.2f} ms/step")
     for e in sorted(kernels, key=lambda e: -e.device_time_total)[:40]:
         print(f"  {e.count / 3:7.1f} x {e.device_time_total / 3e3:8.3f} ms  {e.key[:120]}")
+    # kernel tables of single graphs replayed alone (forward graphs only: the backward graphs gather with buffers that are
+    # only valid inside a live step)
+    s1 = next(iter(tr.net._stage1.values())).graphs
+    s2 = next(iter(tr.net._stage2.values())).graphs
+    for label, g in (("stage 1 forward", s1[0]), ("stage 2 forward", s2[0])):
+        with profile(activities=[ProfilerActivity.CUDA]) as gp:
+            for _ in range(3):
+                g.replay()
+            torch.cuda.synchronize()
+        ks = [e for e in gp.key_averages() if e.device_type == torch.autograd.DeviceType.CUDA]
+        print(f"{label}: {sum(e.count for e in ks) / 3:.0f} nodes, summed device time {sum(e.device_time_total for e in ks) / 3e3:.2f} ms")
+        for e in sorted(ks, key=lambda e: -e.device_time_total)[:22]:
+            print(f"  {e.count / 3:7.1f} x {e.device_time_total / 3e3:8.3f} ms  {e.key[:120]}")
     cpu_ops = sorted([e for e in ev if e.device_type == torch.autograd.DeviceType.CPU], key=lambda e: -e.self_cpu_time_total)[:15]
     print("top host ops (self cpu, per step):")
     for e in cpu_ops:
