@@ -18,7 +18,7 @@ F32, BF16, F64 = 0, 1, 2
 PAD_BORDER, PAD_ZEROS = 0, 1
 FLAG_ASSUME_1D, FLAG_FORCE_GENERIC = 1, 2
 
-_vp, _i, _u, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint, ctypes.c_size_t
+_vp, _i, _u, _sz, _ll = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint, ctypes.c_size_t, ctypes.c_longlong
 
 # name -> (restype, argtypes); mirrors include/msda.h one to one
 SIGNATURES = {
@@ -36,6 +36,8 @@ SIGNATURES = {
     "msda_cap_sample_forward": (_i, [_vp] * 6 + [_i] * 8 + [_i, _i, _u, _vp]),
     "msda_cap_sample_backward": (_i, [_vp] * 9 + [_vp, _sz] + [_i] * 8 + [_i, _i, _u, _vp]),
     "msda_skinny_linear_f32": (_i, [_vp] * 4 + [_i] * 3 + [_vp]),
+    "msda_lstm_cell_forward_f32": (_i, [_vp, _ll] + [_vp] * 5 + [_i, _i, _vp]),
+    "msda_lstm_cell_backward_f32": (_i, [_vp] * 7 + [_i, _i, _vp]),
 }
 
 _lib = None

@@ -719,8 +719,39 @@ int msda_skinny_linear_f32(const float *x, const float *weight, const float *bia
     if (M <= 0 || N <= 0 || K <= 0 || (K & 3)) return MSDA_ERR_SHAPE;
     if (!x || !weight || !y) return MSDA_ERR_NULL;
     if (!aligned16(x) || !aligned16(weight)) return MSDA_ERR_ALIGN;
-    const dim3 grid((N + kSkinnyWarps * kSkinnyNW - 1) / (kSkinnyWarps * kSkinnyNW), (M + kSkinnyRows - 1) / kSkinnyRows);
-    msda_skinny_linear_kernel<<<grid, kSkinnyWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(x, weight, bias, y, M, N, K);
+    const int K4 = K >> 2;
+    const int ks = K4 >= 256 ? 8 : K4 >= 128 ? 4 : K4 >= 64 ? 2 : 1;      // every lane of every slice gets a float4
+    const int per_cta = (kSkinnyWarps / ks) * kSkinnyNW;
+    const dim3 grid((N + per_cta - 1) / per_cta, (M + kSkinnyRows - 1) / kSkinnyRows);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    switch (ks) {
+    case 8: msda_skinny_linear_kernel<8><<<grid, kSkinnyWarps * 32, 0, st>>>(x, weight, bias, y, M, N, K); break;
+    case 4: msda_skinny_linear_kernel<4><<<grid, kSkinnyWarps * 32, 0, st>>>(x, weight, bias, y, M, N, K); break;
+    case 2: msda_skinny_linear_kernel<2><<<grid, kSkinnyWarps * 32, 0, st>>>(x, weight, bias, y, M, N, K); break;
+    default: msda_skinny_linear_kernel<1><<<grid, kSkinnyWarps * 32, 0, st>>>(x, weight, bias, y, M, N, K); break;
+    }
+    return check_launch();
+}
+
+int msda_lstm_cell_forward_f32(const float *pre, long long pre_row_stride, const float *rec, const float *c_prev,
+                               float *c, float *h, float *act, int B, int H, void *stream)
+{
+    g_launches = 0;
+    if (B <= 0 || H <= 0 || pre_row_stride < 4LL * H) return MSDA_ERR_SHAPE;
+    if (!pre || !rec || !c_prev || !c || !h || !act) return MSDA_ERR_NULL;
+    msda_lstm_cell_fwd_kernel<<<(B * H + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        pre, pre_row_stride, rec, c_prev, c, h, act, B, H);
+    return check_launch();
+}
+
+int msda_lstm_cell_backward_f32(const float *grad_h, const float *grad_c, const float *act, const float *c,
+                                const float *c_prev, float *grad_gates, float *grad_c_prev, int B, int H, void *stream)
+{
+    g_launches = 0;
+    if (B <= 0 || H <= 0) return MSDA_ERR_SHAPE;
+    if (!act || !c || !c_prev || !grad_gates || !grad_c_prev) return MSDA_ERR_NULL;
+    msda_lstm_cell_bwd_kernel<<<(B * H + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        grad_h, grad_c, act, c, c_prev, grad_gates, grad_c_prev, B, H);
     return check_launch();
 }
 

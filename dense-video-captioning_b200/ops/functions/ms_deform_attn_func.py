@@ -477,3 +477,40 @@ class _StepLinearFunction(Function):
         grad_w = gs.t().mm(xs) if ctx.needs_input_grad[1] else None
         grad_b = gs.sum(0) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
         return grad_x, grad_w, grad_b, None, None
+
+
+class LSTMCellFunction(Function):
+    """apply(pre, rec, c_prev) -> (h, c): one step of a one-layer nn.LSTM (LSTM_DSA.py:206, :261) given its gate
+    pre-activations split as pre + rec, both (B, 4H) float32 in torch's gate order i,f,g,o; `pre` may be a row-strided
+    view (one word step of a (B, steps, 4H) tensor).  One kernel each way (csrc/msda_steplinear.cuh)."""
+
+    @staticmethod
+    @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    def forward(ctx, pre, rec, c_prev):
+        _check_cuda_contig(rec=rec, c_prev=c_prev)
+        _require(pre.is_cuda and pre.dim() == 2 and pre.stride(1) == 1 and pre.shape == rec.shape, "pre must be (B,4H), unit inner stride")
+        _require(pre.dtype == rec.dtype == c_prev.dtype == torch.float32, "LSTM cell takes float32 tensors")
+        B, H = c_prev.shape
+        _require(rec.shape[1] == 4 * H, "gates must be (B, 4H)")
+        c, h, act = torch.empty_like(c_prev), torch.empty_like(c_prev), torch.empty_like(rec)
+        with torch.cuda.device(rec.device):
+            rc = _lib.lib().msda_lstm_cell_forward_f32(_ptr(pre), pre.stride(0), _ptr(rec), _ptr(c_prev), _ptr(c), _ptr(h),
+                                                       _ptr(act), B, H, _stream(rec.device))
+        _lib.check(rc, "msda_lstm_cell_forward_f32")
+        ctx.save_for_backward(act, c, c_prev)
+        return h, c
+
+    @staticmethod
+    @once_differentiable
+    @torch.amp.custom_bwd(device_type="cuda")
+    def backward(ctx, grad_h, grad_c):
+        act, c, c_prev = ctx.saved_tensors
+        B, H = c_prev.shape
+        grad_h = grad_h.contiguous().float() if grad_h is not None else None
+        grad_c = grad_c.contiguous().float() if grad_c is not None else None
+        grad_gates, grad_c_prev = torch.empty_like(act), torch.empty_like(c_prev)
+        with torch.cuda.device(act.device):
+            rc = _lib.lib().msda_lstm_cell_backward_f32(_ptr(grad_h), _ptr(grad_c), _ptr(act), _ptr(c), _ptr(c_prev),
+                                                        _ptr(grad_gates), _ptr(grad_c_prev), B, H, _stream(act.device))
+        _lib.check(rc, "msda_lstm_cell_backward_f32")
+        return grad_gates, grad_gates, grad_c_prev

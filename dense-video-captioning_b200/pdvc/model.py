@@ -16,17 +16,19 @@ import copy
 import math
 
 from dataclasses import dataclass, field
+from types import SimpleNamespace
 
 import numpy as np
 import torch
 import torch.nn.functional as F
 from torch import nn
 
-from ..ops.functions import StepLinear, get_default_padding_mode
+from ..ops.functions import LSTMCellFunction, StepLinear, get_default_padding_mode
 from ..ops.modules import MSDeformAttnCap
 from .transformer import DeformableTransformer, inverse_sigmoid
 
 
+USE_STEP_LSTM = True       # hoisted input projections + fused cell kernel instead of cuDNN's single-step LSTM
 USE_STEP_LINEAR = True     # few-row kernels + deferred weight gradients for the Linear layers on the caption recurrence
 
 
@@ -201,9 +203,40 @@ class ShowAttendTellCore(nn.Module):
         weight = F.softmax(scores, dim=1)
         attended = torch.bmm(weight.unsqueeze(1), clip.reshape(-1, k, self.att_feat_size)).squeeze(1)
         attended = attended.reshape(n * lq, self.n_heads * self.att_feat_size)
+        if step_linears is not None and "lstm" in step_linears:
+            return step_linears["lstm"](attended, state)
         step_in = torch.cat((xt.unsqueeze(0), attended.unsqueeze(0), query), 2)
         out, state = self.rnn(step_in, state)
         return out.squeeze(0), state
+
+
+class StepLSTM:
+    """The one-layer nn.LSTM of the word step (LSTM_DSA.py:206, :261) over ONE teacher-forced decoding run, same weights:
+    the columns of W_ih that multiply the word embedding and the event query do not depend on the recurrence, so their
+    products are formed for all word steps in one GEMM up front; per step only [attended, h] x [W_ih(attended) | W_hh]
+    (few-row kernel, weight gradient deferred: functions.StepLinear) and the fused cell kernel (functions.LSTMCellFunction)
+    remain -- fp32 throughout, where cuDNN's single-step LSTM spends ~5 kernels forward and ~10 backward per word."""
+
+    def __init__(self, rnn, embedded, query):
+        w_ih, w_hh = rnn.weight_ih_l0, rnn.weight_hh_l0
+        e, c = embedded.shape[-1], query.shape[-1]
+        with torch.autocast("cuda", enabled=False):
+            pre = F.linear(embedded.float(), w_ih[:, :e]) + F.linear(query[0].float(), w_ih[:, e + c:])[:, None, :]
+            recurrent = torch.cat((w_ih[:, e:e + c], w_hh), 1)
+        self.pre = pre.unbind(1)                               # (pairs, 4H) per word step
+        self.rec = StepLinear(SimpleNamespace(weight=recurrent, bias=None))
+        self.i = 0
+
+    @staticmethod
+    def supported(rnn):
+        return rnn.num_layers == 1 and not rnn.bias and not rnn.bidirectional and rnn.weight_ih_l0.dtype == torch.float32
+
+    def __call__(self, attended, state):
+        h_prev, c_prev = state[0][-1], state[1][-1]
+        rec = self.rec(torch.cat((attended.float(), h_prev.float()), 1))
+        h, c = LSTMCellFunction.apply(self.pre[self.i], rec, c_prev)
+        self.i += 1
+        return h, (h.unsqueeze(0), c.unsqueeze(0))
 
 
 class LSTMDSACaptioner(nn.Module):
@@ -289,6 +322,8 @@ class SentenceDecoder:
         if USE_STEP_LINEAR and value.is_cuda and core.att_hid_size > 0 and core.h2att.weight.dtype == torch.float32:
             self.step_linears = {"h2att": StepLinear(core.h2att),
                                  "sampling_offsets": StepLinear(core.deformable_att.sampling_offsets)}
+            if USE_STEP_LSTM and StepLSTM.supported(core.rnn):
+                self.step_linears["lstm"] = StepLSTM(core.rnn, self.embedded, hs)
         self.outputs = []
 
     def step(self, i):

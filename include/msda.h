@@ -196,6 +196,22 @@ int msda_cap_sample_backward(const void *value, const int64_t *temporal_shapes,
 int msda_skinny_linear_f32(const float *x, const float *weight, const float *bias, float *y, int M,
                            int N, int K, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * LSTM cell of the caption head's word step: nn.LSTM with one layer run for one time step
+ * (pdvc/CaptioningHead/LSTM_DSA.py:206, :261), gate order i,f,g,o as in torch's weight layout.
+ *   gates = pre + rec, both (B,4H) f32; pre has row stride pre_row_stride (>= 4H) elements.
+ *   forward : c = f*c_prev + i*g, h = o*tanh(c); act (B,4H) receives the activated gates.
+ *   backward: grad_h / grad_c (B,H), either may be NULL (= 0) -> grad_gates (B,4H) (the gradient of
+ *             pre and of rec alike) and grad_c_prev (B,H).
+ * ------------------------------------------------------------------------------------------- */
+int msda_lstm_cell_forward_f32(const float *pre, long long pre_row_stride, const float *rec,
+                               const float *c_prev, float *c, float *h, float *act, int B, int H,
+                               void *stream);
+
+int msda_lstm_cell_backward_f32(const float *grad_h, const float *grad_c, const float *act,
+                                const float *c, const float *c_prev, float *grad_gates,
+                                float *grad_c_prev, int B, int H, void *stream);
+
 /* Number of kernels the last call on this thread launched (bench.py's gpu_launches). */
 int msda_last_launch_count(void);
 

@@ -575,3 +575,52 @@ def test_step_linear_gradients_match_linear_in_a_recurrence():
     got2 = run(step)                                         # reusable after a complete pass
     for a, b in zip(got2, want):
         assert float((a - b).abs().max()) <= 2e-5 * float(b.abs().max())
+
+
+def test_step_lstm_matches_nn_lstm_float64():
+    """StepLSTM (hoisted input projections + few-row kernel + fused cell kernel) against nn.LSTM run step by step in
+    float64 on the CPU: outputs, final state, gradients of both weight matrices and of every input (rel 2e-5)."""
+    from dense_video_captioning_b200.pdvc.model import StepLSTM
+    torch.manual_seed(4)
+    B, E, C, H, steps = 10, 32, 48, 64, 6
+    rnn = torch.nn.LSTM(E + 2 * C, H, 1, bias=False)
+    ref = torch.nn.LSTM(E + 2 * C, H, 1, bias=False).double()
+    ref.load_state_dict({k: v.double() for k, v in rnn.state_dict().items()})
+    rnn = rnn.cuda()
+    assert StepLSTM.supported(rnn)
+    embedded = torch.randn(B, steps, E)
+    query = torch.randn(1, B, C)
+    attended = torch.randn(steps, B, C)
+    mix = torch.randn(H, C) * 0.3            # makes each step's `attended` depend on the previous hidden state
+
+    def run(module, dev, dtype, stepper):
+        emb = embedded.to(dev, dtype).requires_grad_(True)
+        q = query.to(dev, dtype).requires_grad_(True)
+        att = attended.to(dev, dtype).requires_grad_(True)
+        m = mix.to(dev, dtype)
+        state = (torch.zeros(1, B, H, device=dev, dtype=dtype), torch.zeros(1, B, H, device=dev, dtype=dtype))
+        step = stepper(module, emb, q)
+        outs = []
+        for i in range(steps):
+            a = att[i] + state[0][-1] @ m
+            out, state = step(i, emb, q, a, state)
+            outs.append(out)
+        outs = torch.stack(outs)
+        loss = (outs ** 2).sum() + (state[1] ** 2).sum()
+        grads = torch.autograd.grad(loss, [emb, q, att, module.weight_ih_l0, module.weight_hh_l0])
+        return [outs.detach(), state[1].detach()] + [g for g in grads]
+
+    def ref_stepper(module, emb, q):
+        def step(i, emb, q, a, state):
+            out, state = module(torch.cat((emb[:, i].unsqueeze(0), a.unsqueeze(0), q), 2), state)
+            return out.squeeze(0), state
+        return step
+
+    def new_stepper(module, emb, q):
+        cell = StepLSTM(module, emb, q)
+        return lambda i, emb, q, a, state: cell(a, state)
+
+    want = run(ref, "cpu", torch.float64, ref_stepper)
+    got = run(rnn, "cuda", torch.float32, new_stepper)
+    for g, w in zip(got, want):
+        assert float((g.double().cpu() - w).abs().max()) <= 2e-5 * float(w.abs().max())
