@@ -35,6 +35,8 @@ SIGNATURES = {
     "msda_sample_backward": (_i, [_vp] * 7 + [_vp, _sz] + [_i] * 7 + [_i, _i, _u, _vp]),
     "msda_cap_sample_forward": (_i, [_vp] * 6 + [_i] * 8 + [_i, _i, _u, _vp]),
     "msda_cap_sample_backward": (_i, [_vp] * 9 + [_vp, _sz] + [_i] * 8 + [_i, _i, _u, _vp]),
+    "msda_cap_attend_forward_f32": (_i, [_vp] * 6 + [_i] * 5 + [_vp]),
+    "msda_cap_attend_backward_f32": (_i, [_vp] * 8 + [_i] * 5 + [_vp]),
     "msda_skinny_linear_f32": (_i, [_vp] * 4 + [_i] * 3 + [_vp]),
     "msda_lstm_cell_forward_f32": (_i, [_vp, _ll] + [_vp] * 5 + [_i, _i, _vp]),
     "msda_lstm_cell_backward_f32": (_i, [_vp] * 7 + [_i, _i, _vp]),

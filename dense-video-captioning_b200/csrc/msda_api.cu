@@ -14,6 +14,7 @@
 #include "msda_lean.cuh"
 #include "msda_capsample.cuh"
 #include "msda_steplinear.cuh"
+#include "msda_capattend.cuh"
 
 using namespace msda;
 
@@ -712,6 +713,40 @@ int msda_cap_sample_forward(const void *value, const int64_t *temporal_shapes, c
     return check_launch();
 }
 
+static int attend_check(int BM, int M, int K, int D, int A)
+{
+    if (BM <= 0 || M <= 0 || BM % M || K <= 0 || K > kAttendMaxK || D <= 0 || A <= 0) return MSDA_ERR_SHAPE;
+    return 0;
+}
+
+int msda_cap_attend_forward_f32(const float *samples, const float *hproj, const float *alpha, const float *alpha_bias,
+                                float *attended, float *weight, int BM, int M, int K, int D, int A, void *stream)
+{
+    g_launches = 0;
+    if (int e = attend_check(BM, M, K, D, A)) return e;
+    if (!samples || !hproj || !alpha || !alpha_bias || !attended || !weight) return MSDA_ERR_NULL;
+    AttendArgs a{};
+    a.samples = samples; a.hproj = hproj; a.alpha = alpha; a.alpha_bias = alpha_bias; a.attended = attended; a.weight = weight;
+    a.BM = BM; a.M = M; a.K = K; a.D = D; a.A = A;
+    msda_cap_attend_fwd_kernel<<<BM, kAttendThreads, 0, static_cast<cudaStream_t>(stream)>>>(a);
+    return check_launch();
+}
+
+int msda_cap_attend_backward_f32(const float *samples, const float *hproj, const float *alpha, const float *weight,
+                                 const float *grad_attended, float *grad_samples, float *grad_hproj, float *grad_alpha,
+                                 int BM, int M, int K, int D, int A, void *stream)
+{
+    g_launches = 0;
+    if (int e = attend_check(BM, M, K, D, A)) return e;
+    if (!samples || !hproj || !alpha || !weight || !grad_attended || !grad_samples || !grad_hproj || !grad_alpha) return MSDA_ERR_NULL;
+    AttendArgs a{};
+    a.samples = samples; a.hproj = hproj; a.alpha = alpha; a.weight = const_cast<float *>(weight); a.grad_att = grad_attended;
+    a.grad_samples = grad_samples; a.grad_hproj = grad_hproj; a.grad_alpha = grad_alpha;
+    a.BM = BM; a.M = M; a.K = K; a.D = D; a.A = A;
+    msda_cap_attend_bwd_kernel<<<BM, kAttendThreads, 0, static_cast<cudaStream_t>(stream)>>>(a);
+    return check_launch();
+}
+
 int msda_skinny_linear_f32(const float *x, const float *weight, const float *bias, float *y, int M, int N, int K,
                            void *stream)
 {
@@ -720,16 +755,32 @@ int msda_skinny_linear_f32(const float *x, const float *weight, const float *bia
     if (!x || !weight || !y) return MSDA_ERR_NULL;
     if (!aligned16(x) || !aligned16(weight)) return MSDA_ERR_ALIGN;
     const int K4 = K >> 2;
-    const int ks = K4 >= 256 ? 8 : K4 >= 128 ? 4 : K4 >= 64 ? 2 : 1;      // every lane of every slice gets a float4
+    const int rows = M > 8 ? 16 : 8;
+    const int mtiles = (M + rows - 1) / rows;
+    // K split: every lane of every slice gets a float4, and no more than ~4 CTAs per SM (each CTA should still have work)
+    int ks = K4 >= 256 ? 8 : K4 >= 128 ? 4 : K4 >= 64 ? 2 : 1;
+    while (ks > 1 && (long long)((N + (kSkinnyWarps / ks) * kSkinnyNW - 1) / ((kSkinnyWarps / ks) * kSkinnyNW)) * mtiles > 4 * kNumSMs)
+        ks >>= 1;
     const int per_cta = (kSkinnyWarps / ks) * kSkinnyNW;
-    const dim3 grid((N + per_cta - 1) / per_cta, (M + kSkinnyRows - 1) / kSkinnyRows);
+    const dim3 grid((N + per_cta - 1) / per_cta, mtiles);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    switch (ks) {
-    case 8: msda_skinny_linear_kernel<8><<<grid, kSkinnyWarps * 32, 0, st>>>(x, weight, bias, y, M, N, K); break;
-    case 4: msda_skinny_linear_kernel<4><<<grid, kSkinnyWarps * 32, 0, st>>>(x, weight, bias, y, M, N, K); break;
-    case 2: msda_skinny_linear_kernel<2><<<grid, kSkinnyWarps * 32, 0, st>>>(x, weight, bias, y, M, N, K); break;
-    default: msda_skinny_linear_kernel<1><<<grid, kSkinnyWarps * 32, 0, st>>>(x, weight, bias, y, M, N, K); break;
+#define MSDA_SKINNY(KS_, ROWS_) msda_skinny_linear_kernel<KS_, ROWS_><<<grid, kSkinnyWarps * 32, 0, st>>>(x, weight, bias, y, M, N, K)
+    if (rows == 16) {
+        switch (ks) {
+        case 8: MSDA_SKINNY(8, 16); break;
+        case 4: MSDA_SKINNY(4, 16); break;
+        case 2: MSDA_SKINNY(2, 16); break;
+        default: MSDA_SKINNY(1, 16); break;
+        }
+    } else {
+        switch (ks) {
+        case 8: MSDA_SKINNY(8, 8); break;
+        case 4: MSDA_SKINNY(4, 8); break;
+        case 2: MSDA_SKINNY(2, 8); break;
+        default: MSDA_SKINNY(1, 8); break;
+        }
     }
+#undef MSDA_SKINNY
     return check_launch();
 }
 

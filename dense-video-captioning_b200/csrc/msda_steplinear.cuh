@@ -17,18 +17,19 @@
 
 namespace msda {
 
-constexpr int kSkinnyRows = 8;   // rows of x per CTA (blockIdx.y tiles M)
 constexpr int kSkinnyNW = 2;     // weight rows per warp
 constexpr int kSkinnyWarps = 8;
 
 // KS = warps that share one group of NW weight rows and split K between them (short N / long K: more CTAs, one or two
 // float4 per lane); their partial sums meet in shared memory.
-template <int KS>
+// ROWS = rows of x per CTA (blockIdx.y tiles M): 8, or 16 so that up to 16 rows read the weight once.
+template <int KS, int ROWS>
 __global__ void __launch_bounds__(kSkinnyWarps * 32)
 msda_skinny_linear_kernel(const float *__restrict__ x, const float *__restrict__ w, const float *__restrict__ bias,
                           float *__restrict__ y, int M, int N, int K)
 {
     constexpr int GROUPS = kSkinnyWarps / KS;
+    constexpr int kSkinnyRows = ROWS;
     constexpr int OUT = kSkinnyRows * kSkinnyNW;
     __shared__ float part[GROUPS][KS][OUT];
     const int lane = threadIdx.x & 31;

@@ -514,3 +514,57 @@ class LSTMCellFunction(Function):
                                                         _ptr(grad_gates), _ptr(grad_c_prev), B, H, _stream(act.device))
         _lib.check(rc, "msda_lstm_cell_backward_f32")
         return grad_gates, grad_gates, grad_c_prev
+
+
+class CaptionAttendFunction(Function):
+    """apply(samples, hproj, alpha_weight, alpha_bias, D) -> attended (BM, D).
+
+    Soft attention over the deformable samples of the caption head (LSTM_DSA.py:247-257) in one kernel each way
+    (csrc/msda_capattend.cuh).  samples (BM, K, D + A) float32: per sample the clip feature (D) followed by ctx2att of it
+    (A); hproj (BM // M, A) = h2att(h); alpha_weight (A,) / alpha_bias (1,) = alpha_net."""
+
+    @staticmethod
+    def supported(samples, k):
+        return samples.is_cuda and samples.dtype == torch.float32 and k <= 64
+
+    @staticmethod
+    @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    def forward(ctx, samples, hproj, alpha_weight, alpha_bias, D):
+        samples, hproj = samples.contiguous(), hproj.contiguous()
+        ctx.alpha_shape = alpha_weight.shape
+        alpha_weight, alpha_bias = alpha_weight.contiguous().view(-1), alpha_bias.contiguous().view(-1)
+        _check_cuda_contig(samples=samples, hproj=hproj, alpha_weight=alpha_weight, alpha_bias=alpha_bias)
+        BM, K, row = samples.shape
+        A = row - D
+        _require(A > 0 and alpha_weight.numel() == A and hproj.shape[-1] == A and BM % hproj.shape[0] == 0,
+                 "samples (BM,K,D+A), hproj (B,A), alpha (A,) expected")
+        M = BM // hproj.shape[0]
+        attended = torch.empty((BM, D), dtype=torch.float32, device=samples.device)
+        weight = torch.empty((BM, K), dtype=torch.float32, device=samples.device)
+        with torch.cuda.device(samples.device):
+            rc = _lib.lib().msda_cap_attend_forward_f32(_ptr(samples), _ptr(hproj), _ptr(alpha_weight), _ptr(alpha_bias),
+                                                        _ptr(attended), _ptr(weight), BM, M, K, D, A, _stream(samples.device))
+        _lib.check(rc, "msda_cap_attend_forward_f32")
+        ctx.save_for_backward(samples, hproj, alpha_weight, weight)
+        ctx.dims = (BM, M, K, D, A)
+        return attended
+
+    @staticmethod
+    @once_differentiable
+    @torch.amp.custom_bwd(device_type="cuda")
+    def backward(ctx, grad_attended):
+        samples, hproj, alpha_weight, weight = ctx.saved_tensors
+        BM, M, K, D, A = ctx.dims
+        grad_attended = grad_attended.contiguous().float()
+        grad_samples = torch.empty_like(samples)
+        grad_hproj = torch.empty((BM, A), dtype=torch.float32, device=samples.device)
+        grad_alpha = torch.empty((BM, A + 1), dtype=torch.float32, device=samples.device)
+        with torch.cuda.device(samples.device):
+            rc = _lib.lib().msda_cap_attend_backward_f32(_ptr(samples), _ptr(hproj), _ptr(alpha_weight), _ptr(weight),
+                                                         _ptr(grad_attended), _ptr(grad_samples), _ptr(grad_hproj),
+                                                         _ptr(grad_alpha), BM, M, K, D, A, _stream(samples.device))
+        _lib.check(rc, "msda_cap_attend_backward_f32")
+        if M > 1:
+            grad_hproj = grad_hproj.view(BM // M, M, A).sum(1)
+        total = grad_alpha.sum(0)
+        return grad_samples, grad_hproj, total[:A].view(ctx.alpha_shape), total[A:], None

@@ -23,11 +23,12 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
-from ..ops.functions import LSTMCellFunction, StepLinear, get_default_padding_mode
+from ..ops.functions import CaptionAttendFunction, LSTMCellFunction, StepLinear, get_default_padding_mode
 from ..ops.modules import MSDeformAttnCap
 from .transformer import DeformableTransformer, inverse_sigmoid
 
 
+USE_FUSED_ATTEND = True    # one kernel each way for the soft attention over the samples (csrc/msda_capattend.cuh)
 USE_STEP_LSTM = True       # hoisted input projections + fused cell kernel instead of cuDNN's single-step LSTM
 USE_STEP_LINEAR = True     # few-row kernels + deferred weight gradients for the Linear layers on the caption recurrence
 
@@ -190,18 +191,24 @@ class ShowAttendTellCore(nn.Module):
                                    padding_mask, projected_value=projected_value, **extra)   # (N*M, D', Lq, L, P)
         clip = clip.reshape(n, self.n_heads, -1, lq, k).permute(0, 3, 1, 4, 2)            # (N, Lq, M, L*P, D')
         clip = clip.reshape(n * lq, self.n_heads, k, -1)
+        h2att = step_linears["h2att"] if step_linears is not None else self.h2att
         if clip.shape[-1] == self.att_feat_size + self.att_hid_size:
             # `projected_value` carried ctx2att(value) next to value (SentenceDecoder): interpolation weights sum to 1 in
             # border mode, so sampling the projected rows IS ctx2att of the sampled rows (LSTM_DSA.py:247) without the
             # per-word GEMM, its two backward GEMMs and the per-word weight-gradient accumulation
-            clip, ctx = clip[..., :self.att_feat_size], clip[..., self.att_feat_size:]
+            if USE_FUSED_ATTEND and CaptionAttendFunction.supported(clip, k):
+                attended = CaptionAttendFunction.apply(clip.reshape(n * lq * self.n_heads, k, -1), h2att(state[0][-1]),
+                                                       self.alpha_net.weight, self.alpha_net.bias, self.att_feat_size)
+                clip = None
+            else:
+                clip, ctx = clip[..., :self.att_feat_size], clip[..., self.att_feat_size:]
         else:
             ctx = self.ctx2att(clip)
-        h2att = step_linears["h2att"] if step_linears is not None else self.h2att
-        scores = ctx + h2att(state[0][-1])[:, None, None, :]
-        scores = self.alpha_net(torch.tanh(scores)).view(-1, k)
-        weight = F.softmax(scores, dim=1)
-        attended = torch.bmm(weight.unsqueeze(1), clip.reshape(-1, k, self.att_feat_size)).squeeze(1)
+        if clip is not None:
+            scores = ctx + h2att(state[0][-1])[:, None, None, :]
+            scores = self.alpha_net(torch.tanh(scores)).view(-1, k)
+            weight = F.softmax(scores, dim=1)
+            attended = torch.bmm(weight.unsqueeze(1), clip.reshape(-1, k, self.att_feat_size)).squeeze(1)
         attended = attended.reshape(n * lq, self.n_heads * self.att_feat_size)
         if step_linears is not None and "lstm" in step_linears:
             return step_linears["lstm"](attended, state)

@@ -187,6 +187,26 @@ int msda_cap_sample_backward(const void *value, const int64_t *temporal_shapes,
                              int pad_mode, unsigned flags, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Soft attention over the L*P deformable samples of an event in the caption head
+ * (pdvc/CaptioningHead/LSTM_DSA.py:247-257): score_k = alpha . tanh(ctx_k + hproj) + alpha_bias,
+ * weight = softmax_k(score), attended = sum_k weight_k clip_k.  All f32.
+ *   samples (BM, K, D+A): per sample the D clip channels followed by the A channels of ctx2att(clip)
+ *                         (the sampler run on [value | ctx2att(value)]); BM = events x heads, K <= 64
+ *   hproj (BM/M, A) = h2att(h);  alpha (A,), alpha_bias (1,) = alpha_net
+ *   forward : attended (BM, D), weight (BM, K)
+ *   backward: grad_samples (BM, K, D+A) overwritten; grad_hproj (BM, A) (sum over the M heads is the
+ *             caller's); grad_alpha (BM, A+1): per-(event, head) partials of d alpha and d alpha_bias.
+ * ------------------------------------------------------------------------------------------- */
+int msda_cap_attend_forward_f32(const float *samples, const float *hproj, const float *alpha,
+                                const float *alpha_bias, float *attended, float *weight, int BM, int M,
+                                int K, int D, int A, void *stream);
+
+int msda_cap_attend_backward_f32(const float *samples, const float *hproj, const float *alpha,
+                                 const float *weight, const float *grad_attended, float *grad_samples,
+                                 float *grad_hproj, float *grad_alpha, int BM, int M, int K, int D,
+                                 int A, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Linear layer with a few input rows (the caption head's per-word projections):
  *   y[m,n] = sum_k x[m,k] * weight[n,k] (+ bias[n]);  x (M,K), weight (N,K), y (M,N), all f32,
  *   K % 4 == 0, x and weight 16-byte aligned, bias NULL to skip.  Replaces, for the word loop,

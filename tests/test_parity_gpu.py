@@ -624,3 +624,34 @@ def test_step_lstm_matches_nn_lstm_float64():
     got = run(rnn, "cuda", torch.float32, new_stepper)
     for g, w in zip(got, want):
         assert float((g.double().cpu() - w).abs().max()) <= 2e-5 * float(w.abs().max())
+
+
+@pytest.mark.parametrize("B,M,K,D,A", [(12, 1, 16, 512, 512), (5, 2, 12, 64, 48), (3, 1, 64, 32, 20), (1, 1, 1, 8, 4)])
+def test_caption_attend_matches_torch_float64(B, M, K, D, A):
+    """Fused soft attention over the samples (LSTM_DSA.py:247-257) against the torch expression in float64: output and
+    all four gradients (rel 2e-5)."""
+    from dense_video_captioning_b200.ops.functions import CaptionAttendFunction
+    g = torch.Generator().manual_seed(9)
+    samples = torch.randn(B * M, K, D + A, generator=g)
+    hproj = torch.randn(B, A, generator=g)
+    alpha_w = torch.randn(1, A, generator=g) * 0.3
+    alpha_b = torch.randn(1, generator=g)
+    grad = torch.randn(B * M, D, generator=g)
+
+    def run(dev, dtype, fused):
+        s, h, w, b = (t.to(dev, dtype).requires_grad_(True) for t in (samples, hproj, alpha_w, alpha_b))
+        if fused:
+            out = CaptionAttendFunction.apply(s, h, w, b, D)
+        else:
+            clip, ctx = s[..., :D], s[..., D:]
+            scores = torch.tanh(ctx + h.repeat_interleave(M, 0)[:, None, :]) @ w.t() + b          # (BM, K, 1)
+            out = (torch.softmax(scores.squeeze(-1), 1)[:, :, None] * clip).sum(1)
+        grads = torch.autograd.grad(out, [s, h, w, b], grad.to(dev, dtype))
+        return [out.detach()] + list(grads)
+
+    want = run("cpu", torch.float64, False)
+    got = run("cuda", torch.float32, True)
+    for name, a, b in zip(("attended", "grad_samples", "grad_hproj", "grad_alpha", "grad_alpha_bias"), got, want):
+        scale = max(float(b.abs().max()), 1.0 if name == "grad_alpha_bias" else 0.0)
+        assert a.shape == b.shape, name
+        assert float((a.double().cpu() - b).abs().max()) <= 2e-5 * scale, name
