@@ -716,6 +716,7 @@ int msda_cap_sample_forward(const void *value, const int64_t *temporal_shapes, c
 static int attend_check(int BM, int M, int K, int D, int A)
 {
     if (BM <= 0 || M <= 0 || BM % M || K <= 0 || K > kAttendMaxK || D <= 0 || A <= 0) return MSDA_ERR_SHAPE;
+    if ((D & 3) || (A & 3) || D > 3072 || A > 1536) return MSDA_ERR_UNSUPPORTED;      // float4 rows, <= 48 KB of partial sums
     return 0;
 }
 
@@ -728,7 +729,8 @@ int msda_cap_attend_forward_f32(const float *samples, const float *hproj, const 
     AttendArgs a{};
     a.samples = samples; a.hproj = hproj; a.alpha = alpha; a.alpha_bias = alpha_bias; a.attended = attended; a.weight = weight;
     a.BM = BM; a.M = M; a.K = K; a.D = D; a.A = A;
-    msda_cap_attend_fwd_kernel<<<BM, kAttendThreads, 0, static_cast<cudaStream_t>(stream)>>>(a);
+    if (!aligned16(samples) || !aligned16(hproj) || !aligned16(alpha) || !aligned16(attended)) return MSDA_ERR_ALIGN;
+    msda_cap_attend_fwd_kernel<<<BM, kAttendThreads, sizeof(float) * kAttendKG * D, static_cast<cudaStream_t>(stream)>>>(a);
     return check_launch();
 }
 
@@ -743,7 +745,10 @@ int msda_cap_attend_backward_f32(const float *samples, const float *hproj, const
     a.samples = samples; a.hproj = hproj; a.alpha = alpha; a.weight = const_cast<float *>(weight); a.grad_att = grad_attended;
     a.grad_samples = grad_samples; a.grad_hproj = grad_hproj; a.grad_alpha = grad_alpha;
     a.BM = BM; a.M = M; a.K = K; a.D = D; a.A = A;
-    msda_cap_attend_bwd_kernel<<<BM, kAttendThreads, 0, static_cast<cudaStream_t>(stream)>>>(a);
+    if (!aligned16(samples) || !aligned16(hproj) || !aligned16(alpha) || !aligned16(grad_attended) || !aligned16(grad_samples) ||
+        !aligned16(grad_hproj))
+        return MSDA_ERR_ALIGN;
+    msda_cap_attend_bwd_kernel<<<BM, kAttendThreads, sizeof(float) * 2 * kAttendKG * A, static_cast<cudaStream_t>(stream)>>>(a);
     return check_launch();
 }
 

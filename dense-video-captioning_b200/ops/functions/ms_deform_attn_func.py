@@ -524,8 +524,10 @@ class CaptionAttendFunction(Function):
     (A); hproj (BM // M, A) = h2att(h); alpha_weight (A,) / alpha_bias (1,) = alpha_net."""
 
     @staticmethod
-    def supported(samples, k):
-        return samples.is_cuda and samples.dtype == torch.float32 and k <= 64
+    def supported(samples, k, d):
+        a = samples.shape[-1] - d
+        return (samples.is_cuda and samples.dtype == torch.float32 and k <= 64 and d % 4 == 0 and a % 4 == 0
+                and d <= 3072 and 0 < a <= 1536)
 
     @staticmethod
     @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)

@@ -196,7 +196,7 @@ class ShowAttendTellCore(nn.Module):
             # `projected_value` carried ctx2att(value) next to value (SentenceDecoder): interpolation weights sum to 1 in
             # border mode, so sampling the projected rows IS ctx2att of the sampled rows (LSTM_DSA.py:247) without the
             # per-word GEMM, its two backward GEMMs and the per-word weight-gradient accumulation
-            if USE_FUSED_ATTEND and CaptionAttendFunction.supported(clip, k):
+            if USE_FUSED_ATTEND and CaptionAttendFunction.supported(clip, k, self.att_feat_size):
                 attended = CaptionAttendFunction.apply(clip.reshape(n * lq * self.n_heads, k, -1), h2att(state[0][-1]),
                                                        self.alpha_net.weight, self.alpha_net.bias, self.att_feat_size)
                 clip = None

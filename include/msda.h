@@ -191,7 +191,8 @@ int msda_cap_sample_backward(const void *value, const int64_t *temporal_shapes,
  * (pdvc/CaptioningHead/LSTM_DSA.py:247-257): score_k = alpha . tanh(ctx_k + hproj) + alpha_bias,
  * weight = softmax_k(score), attended = sum_k weight_k clip_k.  All f32.
  *   samples (BM, K, D+A): per sample the D clip channels followed by the A channels of ctx2att(clip)
- *                         (the sampler run on [value | ctx2att(value)]); BM = events x heads, K <= 64
+ *                         (the sampler run on [value | ctx2att(value)]); BM = events x heads, K <= 64,
+ *                         D % 4 == 0 <= 3072, A % 4 == 0 <= 1536, 16-byte aligned buffers
  *   hproj (BM/M, A) = h2att(h);  alpha (A,), alpha_bias (1,) = alpha_net
  *   forward : attended (BM, D), weight (BM, K)
  *   backward: grad_samples (BM, K, D+A) overwritten; grad_hproj (BM, A) (sum over the M heads is the
