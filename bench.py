@@ -479,9 +479,13 @@ def pdvc_train_leg(args, world, rank, device):
         start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         start.record()
-        last = None
+        last, pending = None, None
         for i in range(args.pdvc_steps):
-            last = float(tr.step(videos[i % len(videos)]))      # device->host read of the step's loss
+            loss = tr.step(videos[i % len(videos)])
+            if pending is not None:
+                last = float(pending)       # device->host read of every step's loss, one step late: the host issues
+            pending = loss                  # step i+1 (input copy, stage-1 graph launch) while the GPU finishes step i
+        last = float(pending)
         end.record()
         torch.cuda.synchronize()
         wall = time.perf_counter() - t0

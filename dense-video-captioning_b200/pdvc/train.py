@@ -134,7 +134,8 @@ class Trainer:
         self.weight_dict = self.criterion.weight_dict
 
     def step(self, host_batch):
-        """One training iteration on one video; returns the (device) total loss without synchronising."""
+        """One training iteration on one video; returns the total loss as a device scalar of its own (not a view of a
+        graph's static output) without synchronising, so a caller may read step i's loss after issuing step i+1."""
         dt = to_device(host_batch, self.device)
         self.optimizer.zero_grad(set_to_none=True)
         if self.mode == "eager":
@@ -152,7 +153,7 @@ class Trainer:
         torch.nn.utils.clip_grad_norm_(self.params, self.grad_clip)
         self.optimizer.step()
         self.last_losses = losses
-        return total.detach()
+        return total.detach().clone()
 
 
 class _StepModule(torch.nn.Module):
