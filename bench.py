@@ -469,7 +469,7 @@ def pdvc_train_leg(args, world, rank, device):
     names = args.pdvc_configs.split(",") if args.pdvc_configs else list(CONFIGS)
     res = {}
     for name in names:
-        tr = Trainer(name, device, world_size=world)
+        tr = Trainer(name, device, world_size=world, sync=args.pdvc_sync)
         videos = [synthetic_video(tr.cfg, tr.n_gt, tr.cap_len, seed=7919 * i + rank) for i in range(8)]
         for i in range(args.pdvc_warmup):
             tr.step(videos[i % len(videos)])
@@ -600,7 +600,7 @@ def run_ours(args, world, rank, local):
     if not args.no_pdvc:
         try:
             line["pdvc_train"] = {"metric": "pdvc_train_videos_per_s", "n_gpus": world, "data": "synthetic",
-                                  "parallelism": f"ddp{world} (NCCL gradient all-reduce, 1 video per rank per step)" if world > 1
+                                  "parallelism": f"dp{world} (NCCL gradient all-reduce: {args.pdvc_sync}; 1 video per rank per step)" if world > 1
                                   else "single process", "configs": pdvc_train_leg(args, world, rank, device)}
         except Exception as ex:
             if world > 1:
@@ -684,6 +684,8 @@ def main():
     ap.add_argument("--pdvc-steps", type=int, default=30)
     ap.add_argument("--pdvc-warmup", type=int, default=5)
     ap.add_argument("--pdvc-configs", default="", help="comma-separated subset of pdvc.CONFIGS (default: all)")
+    ap.add_argument("--pdvc-sync", default="flat", choices=["flat", "ddp"],
+                    help="gradient exchange at N>1: one flat all-reduce after backward, or torch DDP")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.sweep:

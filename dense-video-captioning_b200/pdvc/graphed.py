@@ -324,9 +324,11 @@ class StagedStep(nn.Module):
         if use_graphs:      # the matching costs are part of stage 1, so its graph depends on the event count too
             key1 = (int(vf.shape[1]), int(target['boxes'].shape[0]))
             stage1 = self._cached(self._stage1, key1, lambda: self._graph(self.stage1, tuple(a.detach().clone() for a in args1)))
+        # the event count is host data: its all-reduce (criterion.py:169-171) is issued before stage 1 and has long
+        # finished when stage 2 reads it, instead of making the ranks meet in the middle of the step
+        num_boxes = self._num_boxes(int(target['boxes'].shape[0]), vf.device)
         hs, init_ref, inter_refs, logits, counts, boxes, memory, mask_flat, valid_ratios, costs = stage1(*args1)
         n_pred = hs.shape[0]
-        num_boxes = self._num_boxes(int(target['boxes'].shape[0]), vf.device)
         q_host, t_host = self._match(costs, n_pred)
         cap_host = dt.get('cap_tensor_host')
         cap_host = dt['cap_tensor'].cpu().numpy() if cap_host is None else np.asarray(cap_host)

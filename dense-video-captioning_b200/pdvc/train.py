@@ -81,9 +81,13 @@ class Trainer:
     """model + criterion + Adam(lr 5e-5, wd 1e-4) + grad clip 100 (cfgs/anet_c3d_pdvcl.yml:17,21; opts.py:104-105)."""
 
     def __init__(self, name_or_cfg, device, world_size=1, lr=5e-5, weight_decay=1e-4, grad_clip=100.0, amp=None,
-                 seed=0, dropout=None, mode="graphs"):
+                 seed=0, dropout=None, mode="graphs", sync="flat"):
         """mode: 'graphs' = two CUDA graphs around the host matcher (pdvc/graphed.py; CUDA only), 'staged' = the same
-        two stages eagerly, 'eager' = the reference's control flow (model.forward with the criterion inside)."""
+        two stages eagerly, 'eager' = the reference's control flow (model.forward with the criterion inside).
+        sync (world_size > 1): 'flat' = gradients gathered into one buffer and all-reduced in ONE collective after
+        backward (the two-graph step hands all gradients over at the end of its two backward replays, so there is little
+        for DDP's bucket overlap to hide, while its per-parameter hooks cost one copy kernel per parameter); 'ddp' =
+        torch DistributedDataParallel."""
         spec = CONFIGS[name_or_cfg] if isinstance(name_or_cfg, str) else dict(cfg=name_or_cfg, n_gt=4, cap_len=12, amp=False)
         cfg = spec["cfg"]
         if dropout is not None:
@@ -116,7 +120,12 @@ class Trainer:
         else:
             from .graphed import StagedStep
             self.net = StagedStep(self.model, self.criterion, graphs=(mode == "graphs"), amp=self.amp)
-        if world_size > 1:
+        self.world_size, self.sync = world_size, sync
+        if world_size > 1 and sync == "flat":
+            with torch.no_grad():                    # what DDP's constructor does: rank 0's weights and buffers everywhere
+                for t in list(self.model.parameters()) + list(self.model.buffers()):
+                    torch.distributed.broadcast(t, 0)
+        elif world_size > 1:
             from torch.nn.parallel import DistributedDataParallel as DDP
             ids = [self.device.index] if self.device.type == "cuda" else None
             if self.device.type == "cuda":
@@ -150,10 +159,30 @@ class Trainer:
             else:
                 total, losses, _ = self.net(dt)       # graphs: autocast is baked into the captured stages
         total.backward()
+        if self.world_size > 1 and self.sync == "flat":
+            self._allreduce_gradients()
         torch.nn.utils.clip_grad_norm_(self.params, self.grad_clip)
         self.optimizer.step()
         self.last_losses = losses
         return total.detach().clone()
+
+    def _allreduce_gradients(self):
+        """Mean of the gradients over the ranks: one concatenation, one all-reduce, .grad re-pointed into the flat buffer."""
+        if getattr(self, "_flat", None) is None:
+            self._flat = torch.empty(sum(p.numel() for p in self.params), dtype=self.params[0].dtype, device=self.device)
+            self._flat_views, offset = [], 0
+            for p in self.params:
+                self._flat_views.append(self._flat[offset:offset + p.numel()].view_as(p))
+                offset += p.numel()
+        grads = [p.grad if p.grad is not None else torch.zeros_like(p) for p in self.params]
+        torch.cat([g.reshape(-1) for g in grads], out=self._flat)
+        if torch.distributed.get_backend() == "nccl":
+            torch.distributed.all_reduce(self._flat, op=torch.distributed.ReduceOp.AVG)
+        else:
+            torch.distributed.all_reduce(self._flat)
+            self._flat.div_(self.world_size)
+        for p, view in zip(self.params, self._flat_views):
+            p.grad = view
 
 
 class _StepModule(torch.nn.Module):

@@ -30,7 +30,8 @@ def graph_us(fn, reps=64):
     return a.elapsed_time(b) * 1e3 / (20 * reps)
 
 
-for M, N, K in [(12, 512, 512), (12, 16, 1024), (12, 1024, 16), (4, 512, 512), (30, 512, 512), (12, 2048, 1024), (12, 1608, 512)]:
+for M, N, K in [(12, 512, 512), (12, 16, 1024), (12, 1024, 16), (4, 512, 512), (30, 512, 512), (12, 2048, 1024), (12, 1608, 512),
+                (100, 512, 512), (375, 512, 512), (100, 256, 512), (375, 2048, 512)]:
     x = torch.randn(M, K, device="cuda")
     w = torch.randn(N, K, device="cuda")
     b = torch.randn(N, device="cuda")
