@@ -4,6 +4,7 @@ import os
 import socket
 import sys
 
+import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
@@ -62,7 +63,7 @@ def _patch_cuda_modules_with_oracle():
     MSDeformAttnCap.forward = cap_forward
 
 
-def _ddp_worker(rank, world, port, out):
+def _ddp_worker(rank, world, port, out, sync):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
                       LOCAL_RANK=str(rank))
     sys.path.insert(0, ROOT)
@@ -72,7 +73,7 @@ def _ddp_worker(rank, world, port, out):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     cfg = PDVCConfig(feature_dim=64, num_queries=6, frame_embedding_num=32, vocab_size=40, transformer_ff_dim=128,
                      enc_layers=1, dec_layers=2, transformer_dropout_prob=0.0, drop_prob=0.0)
-    tr = Trainer(cfg, "cpu", world_size=world, lr=1e-3)
+    tr = Trainer(cfg, "cpu", world_size=world, lr=1e-3, sync=sync)
     before = torch.cat([p.detach().flatten() for p in tr.params]).clone()
     losses = []
     for step in range(2):
@@ -86,11 +87,13 @@ def _ddp_worker(rank, world, port, out):
     dist.destroy_process_group()
 
 
-def test_two_rank_ddp_training_keeps_replicas_identical():
+@pytest.mark.parametrize("sync", ["flat", "ddp"])
+def test_two_rank_ddp_training_keeps_replicas_identical(sync):
+    """Both gradient-exchange modes of the Trainer: one flat all-reduce after backward, and torch DDP."""
     world = 2
     mgr = mp.Manager()
     out = mgr.dict()
-    mp.spawn(_ddp_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    mp.spawn(_ddp_worker, args=(world, _free_port(), out, sync), nprocs=world, join=True)
     assert out[0][3] == out[1][3]                        # identical initial weights (seeded)
     assert out[0][0] != out[1][0]                        # different videos -> different losses
     assert out[0][1] > 0 and out[1][1] > 0               # the step moved the parameters
