@@ -18,6 +18,7 @@ Shape key of stage 2: (events, matched pairs, word steps per layer) -- a new key
 `graphs=False` runs the same two stages eagerly (used by the CPU tests and as the reference for the graph tests).
 """
 import contextlib
+import gc
 
 import numpy as np
 import torch
@@ -68,11 +69,21 @@ def graph_module(module, sample_args, warmup=3, autocast=None):
 
     pool = torch.cuda.graph_pool_handle()
     fwd_graph, bwd_graph = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
-    with torch.cuda.graph(fwd_graph, pool=pool, capture_error_mode="thread_local"):
-        static_outs = run()
-    static_grad_outs = tuple(torch.zeros_like(o) if o.requires_grad else None for o in static_outs)
-    with torch.cuda.graph(bwd_graph, pool=pool, capture_error_mode="thread_local"):
-        grads = backward_of(static_outs, static_grad_outs)
+    # No cyclic garbage collection while a capture is open: a collection that happens to run mid-capture may destroy CUDA
+    # graphs / pools of an earlier Trainer or of evicted shape keys, and the driver calls that makes invalidate the capture
+    # ("operation failed due to a previous error during capture").  torch.cuda.graph collects once on entry only.
+    gc_was_enabled = gc.isenabled()
+    gc.collect()
+    gc.disable()
+    try:
+        with torch.cuda.graph(fwd_graph, pool=pool, capture_error_mode="thread_local"):
+            static_outs = run()
+        static_grad_outs = tuple(torch.zeros_like(o) if o.requires_grad else None for o in static_outs)
+        with torch.cuda.graph(bwd_graph, pool=pool, capture_error_mode="thread_local"):
+            grads = backward_of(static_outs, static_grad_outs)
+    finally:
+        if gc_was_enabled:
+            gc.enable()
     grads = list(grads)
     static_grad_inputs = tuple(grads.pop(0) if t.requires_grad else None for t in surface)
     n_user = len(sample_args)

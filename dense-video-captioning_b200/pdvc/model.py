@@ -28,6 +28,7 @@ from ..ops.modules import MSDeformAttnCap
 from .transformer import DeformableTransformer, inverse_sigmoid
 
 
+USE_FP32_SAMPLES = True    # bf16 autocast: caption-head samples (two projected-memory rows per sample) kept in fp32
 USE_FUSED_ATTEND = True    # one kernel each way for the soft attention over the samples (csrc/msda_capattend.cuh)
 USE_STEP_LSTM = True       # hoisted input projections + fused cell kernel instead of cuDNN's single-step LSTM
 USE_STEP_LINEAR = True     # few-row kernels + deferred weight gradients for the Linear layers on the caption recurrence
@@ -323,6 +324,8 @@ class SentenceDecoder:
         value = core.deformable_att.project_value(memory, mask)                           # once per sentence, not per word
         if value.is_cuda and core.att_hid_size > 0 and (core.deformable_att.padding_mode or get_default_padding_mode()) == "border":
             value = torch.cat((value, core.ctx2att(value)), -1)                           # see ShowAttendTellCore.forward
+            if USE_FP32_SAMPLES and USE_FUSED_ATTEND and value.dtype == torch.bfloat16:
+                value = value.float()       # under bf16 autocast: sample in fp32 so that the fused attention kernel applies
         self.value = value.contiguous()
         self.embedded = head.embed(seq)                     # teacher forcing: every input word is known up front
         self.step_linears = None
