@@ -341,8 +341,9 @@ def time_e2e(w, steps, warmup, world, chunk=8):
     MSDeformAttnFusedFunction.apply + backward per batch chunk, overlapping the copy-in of the next chunk and the
     copy-out of the previous one with the kernels.  Every byte of the step's inputs and results crosses the host link
     inside the timed region."""
-    from dense_video_captioning_b200.ops.host_pipeline import HostPipelinedFusedMSDA
+    from dense_video_captioning_b200.ops.host_pipeline import HostPipelinedFusedMSDA, bind_host_to_gpu_numa_node
     dev = w["value"].device
+    time_e2e.numa = bind_host_to_gpu_numa_node(dev)        # pinned buffers below are first-touched on the GPU's node
     host_in = [w[k].cpu().pin_memory() for k in ("value", "ref", "off", "logits", "grad_out")]
     h2d = sum(t.numel() * t.element_size() for t in host_in)
     pipe = HostPipelinedFusedMSDA(w["shapes"], w["lsi"], dev, chunk=chunk)
@@ -590,7 +591,7 @@ def run_ours(args, world, rank, local):
         "dtype": "bf16" if args.dtype == "bf16" else "f32", "data": "synthetic",
         "config": workload_config(cfg, world), "roofline": roof, "clocks": clocks,
         "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
+                "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "host_numa": getattr(time_e2e, "numa", None),
                 "api": "ops.host_pipeline.HostPipelinedFusedMSDA (MSDeformAttnFusedFunction.apply + backward per 8-video chunk; copy-in, kernels and copy-out on three streams), pinned host tensors in and out"},
         "gpu_launches": launches,
         "hbm_gbs_fwd_bwd": roof["fwd_bwd"]["achieved"],

@@ -12,6 +12,34 @@ import torch
 from .functions.ms_deform_attn_func import MSDeformAttnFusedFunction
 
 
+def bind_host_to_gpu_numa_node(device):
+    """Run this process (and with it the first-touch placement of the pinned buffers it allocates next) on the CPUs of the
+    NUMA node the GPU hangs off, so that host<->device DMA does not cross the socket interconnect.  Returns a dict saying
+    what was found and done; never raises (containers may hide sysfs or forbid sched_setaffinity)."""
+    import os
+    info = {"numa_node": None, "bound": False}
+    try:
+        p = torch.cuda.get_device_properties(torch.device(device))
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        info["pci"] = bdf
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        info["numa_node"] = node
+        if node < 0:
+            return info
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = cpus & os.sched_getaffinity(0)
+        info["node_cpus"], info["allowed_before"] = len(cpus), len(os.sched_getaffinity(0))
+        if allowed and allowed != os.sched_getaffinity(0):
+            os.sched_setaffinity(0, allowed)
+            info["bound"] = True
+    except Exception as ex:                                 # noqa: BLE001 -- diagnostic only
+        info["error"] = repr(ex)[:120]
+    return info
+
+
 class HostPipelinedFusedMSDA:
     """fwd+bwd of MSDeformAttnFusedFunction with pinned host tensors in and out.
 
