@@ -120,6 +120,8 @@ def graph_module(module, sample_args, warmup=3, autocast=None):
     return call
 
 
+ALIAS_STAGE_INPUTS = True     # stage 2 reads stage 1's static output buffers directly
+
 LOSS_TERMS = ("loss_ce", "loss_counter", "loss_bbox", "loss_giou", "loss_self_iou", "cardinality_error", "loss_caption")
 
 
@@ -353,7 +355,10 @@ class StagedStep(nn.Module):
             lengths = pyramid_lengths(vf.shape[1], self.model.cfg.num_feature_levels)
             stage2 = LossStage(self.model, self.criterion, n_steps, lengths)
             if use_graphs:
-                sample = tuple(a.detach().clone().requires_grad_(a.requires_grad) for a in args2)
+                # the first 9 arguments are static outputs of the stage-1 graph: captured in place (same storage), so the
+                # replay wrapper finds identical addresses and skips its input copies; everything else is cloned
+                sample = tuple((a.detach() if (ALIAS_STAGE_INPUTS and i < 9) else a.detach().clone()).requires_grad_(a.requires_grad)
+                               for i, a in enumerate(args2))
                 stage2 = self._graph(stage2, sample)
             return stage2
 
