@@ -216,3 +216,20 @@ def test_graph_trainer_tracks_eager_trainer_over_changing_shapes():
             assert len(tr.net._stage2) == 4            # (2,4) (5,7) (3,4) (3,6)
     for a, b in zip(runs["staged"], runs["graphs"]):
         assert np.isfinite(b) and abs(a - b) <= 2e-3 * abs(a), (runs["staged"], runs["graphs"])
+
+
+@pytest.mark.gpu
+def test_bf16_autocast_trainer_tracks_fp32_trainer():
+    """The bf16-autocast configuration against the same model trained in fp32, two trainers one after
+    the other in one process: first-step loss within 5 % (bf16 GEMMs; the caption-head samples, the few-row products, the
+    LSTM cell and the fused attention stay fp32), every loss finite, and the loss goes down on a repeated video."""
+    from dense_video_captioning_b200.pdvc import Trainer, synthetic_video
+    losses = {}
+    for amp in (False, True):
+        tr = Trainer("yc2_newmodel_core_bf16", "cuda:0", amp=amp, dropout=0.0, seed=5)
+        video = synthetic_video(tr.cfg, tr.n_gt, tr.cap_len, seed=11)
+        losses[amp] = [float(tr.step(video)) for _ in range(5)]
+        del tr
+    assert all(np.isfinite(v) for v in losses[False] + losses[True]), losses
+    assert abs(losses[True][0] - losses[False][0]) <= 0.05 * abs(losses[False][0]), losses
+    assert losses[True][-1] < losses[True][0] and losses[False][-1] < losses[False][0], losses
