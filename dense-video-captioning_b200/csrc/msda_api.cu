@@ -247,7 +247,7 @@ template <bool FUSED, bool BWD> int launch_tile(const TileArgs &a, const TilePla
 
 struct LeanPlan {
     bool ok;
-    int lpg, nch, lpa, spl, Q, chunks, win_rows, gridK;
+    int lpg, nch, lpa, spl, Q, chunks, win_rows, gridK, hist_cap;
     size_t smem;
 };
 
@@ -286,10 +286,13 @@ LeanPlan lean_plan(const Dims &d, int dtype, bool backward)
         static const int bwin_kb = env_int("MSDA_BWIN_KB", 34);
         p.win_rows = bwin_kb * 1024 / rb;
         if (p.win_rows > d.S + d.L) p.win_rows = d.S + d.L;
-        p.smem = bwd_lean_smem_bytes(p.Q, p.lpa * p.spl, d.S, rb, p.win_rows);
+        // sort histogram: level-grid tiles touch one short window per level (no more rows than the value window
+        // holds); tiles of consecutive queries may touch the whole slice.  Tiles that exceed it are swept unsorted.
+        p.hist_cap = p.gridK ? (p.win_rows < d.S ? p.win_rows : d.S) : (d.S < 8192 ? d.S : 8192);
+        p.smem = bwd_lean_smem_bytes(p.Q, p.lpa * p.spl, p.hist_cap, rb, p.win_rows);
         if (p.smem > kMaxDynSmem) {   // no room for a window: gather value rows through L1
             p.win_rows = 0;
-            p.smem = bwd_lean_smem_bytes(p.Q, p.lpa * p.spl, d.S, rb, 0);
+            p.smem = bwd_lean_smem_bytes(p.Q, p.lpa * p.spl, p.hist_cap, rb, 0);
         }
         if (p.smem > kMaxDynSmem) return p;
     } else {
@@ -315,6 +318,7 @@ void fill_lean_args(TileArgs &a, const Dims &d, const LeanPlan &p, int pad_mode)
     a.chunks = p.chunks;
     a.win_rows = p.win_rows;
     a.gridK = p.gridK;
+    a.hist_cap = p.hist_cap;
 }
 
 template <typename VT, int LPG, int NCH, int LPA, bool FUSED, bool BWD, int SPL = 1>

@@ -56,6 +56,7 @@ struct TileArgs {
     int chunks;    // ceil(Lq / Q)
     int win_rows;  // forward: capacity of the shared-memory value window in rows (0: never stage)
     int gridK;     // lean kernels: 0 = a tile is Q consecutive queries; K > 0 = level-grid tiling into K time spans
+    int hist_cap;  // lean backward: rows the sort histogram holds (a tile touching more is swept unsorted)
 };
 
 // ---- small PTX wrappers -------------------------------------------------------------------

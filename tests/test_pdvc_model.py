@@ -18,14 +18,27 @@ from conftest import load_golden
 from oracle import core_pytorch
 
 
+# fixtures written by tests/golden/make_golden_pdvc.py from the unmodified reference model:
+#   anet_c3d       cfgs/anet_c3d_pdvc.yml                                   (BASELINE configs[2])
+#   yc2shape       cfgs/yc2_tsp_pdvc.yml with the YouCook2 shapes            (BASELINE configs[1](b): 100 queries, T = 200)
+#   newmodel_core  cfgs/yc2_newModel_sound.yml:8-19, 3+3 layers, 768-d      (BASELINE configs[3])
+FIXTURES = ["anet_c3d", "yc2shape", "newmodel_core"]
+
+
 def _cfg(golden):
     from dense_video_captioning_b200.pdvc import PDVCConfig
+    if "config" in golden:
+        fd, nq, T, mes, enc, dec, hid, ff = (int(v) for v in golden["config"])
+        return PDVCConfig(feature_dim=fd, num_queries=nq, frame_embedding_num=T, vocab_size=int(golden["vocab_size"]),
+                          max_eseq_length=mes, enc_layers=enc, dec_layers=dec, hidden_dim=hid, transformer_ff_dim=ff,
+                          transformer_dropout_prob=0.0, drop_prob=0.0)
     return PDVCConfig(feature_dim=500, num_queries=10, frame_embedding_num=100, vocab_size=int(golden["vocab_size"]),
                       max_eseq_length=10, transformer_dropout_prob=0.0, drop_prob=0.0)
 
 
-def _batch(cfg, dtype, device):
-    b = cases.pdvc_batch(5, cfg.frame_embedding_num, cfg.feature_dim, n_gt=4, cap_len=9, vocab_size=cfg.vocab_size)
+def _batch(cfg, dtype, device, golden=None):
+    seed, n_gt, cap_len = (int(v) for v in golden["batch"]) if golden is not None and "batch" in golden else (5, 4, 9)
+    b = cases.pdvc_batch(seed, cfg.frame_embedding_num, cfg.feature_dim, n_gt=n_gt, cap_len=cap_len, vocab_size=cfg.vocab_size)
     t = {k: torch.from_numpy(v) for k, v in b.items()}
     f = lambda x: x.to(dtype).to(device)  # noqa: E731
     return {"video_tensor": f(t["video_tensor"]), "video_mask": t["video_mask"].to(device),
@@ -86,9 +99,10 @@ def oracle_modules(monkeypatch):
     monkeypatch.setattr(MSDeformAttnCap, "forward", cap_forward)
 
 
-def test_host_logic_matches_reference_model_float64(oracle_modules):
+@pytest.mark.parametrize("fixture", FIXTURES)
+def test_host_logic_matches_reference_model_float64(oracle_modules, fixture):
     from dense_video_captioning_b200.pdvc import build
-    golden = load_golden("pdvc_anet_c3d")
+    golden = load_golden("pdvc_" + fixture)
     prev = torch.get_default_dtype()
     torch.set_default_dtype(torch.float64)
     try:
@@ -96,7 +110,7 @@ def test_host_logic_matches_reference_model_float64(oracle_modules):
         model, criterion = build(cfg)
         model.double().train()
         cases.fill_parameters(model)
-        out, loss, total = _run(model, criterion, _batch(cfg, torch.float64, "cpu"))
+        out, loss, total = _run(model, criterion, _batch(cfg, torch.float64, "cpu", golden))
         _check(golden, model, out, loss, total, rel_loss=1e-9, rel_grad=1e-7)
     finally:
         torch.set_default_dtype(prev)
@@ -148,33 +162,66 @@ def test_state_dict_keys_follow_the_reference():
 
 
 @pytest.mark.gpu
-def test_cuda_model_matches_reference_model_fp32():
+@pytest.mark.parametrize("fixture", FIXTURES)
+def test_cuda_model_matches_reference_model_fp32(fixture):
     from dense_video_captioning_b200.pdvc import build
-    golden = load_golden("pdvc_anet_c3d")
+    golden = load_golden("pdvc_" + fixture)
     cfg = _cfg(golden)
     model, criterion = build(cfg)
     model.cuda().train()
     criterion.cuda()
     cases.fill_parameters(model)
-    out, loss, total = _run(model, criterion, _batch(cfg, torch.float32, "cuda"))
+    out, loss, total = _run(model, criterion, _batch(cfg, torch.float32, "cuda", golden))
     torch.cuda.synchronize()
     # fp32 model vs float64 reference: losses to 2e-4 relative, parameter-gradient norms to 2e-3
     _check(golden, model, out, loss, total, rel_loss=2e-4, rel_grad=2e-3)
 
 
 @pytest.mark.gpu
-def test_cuda_graph_step_matches_reference_model_fp32():
+@pytest.mark.parametrize("fixture", ["yc2shape", "newmodel_core"])
+def test_cuda_model_bf16_autocast_tracks_reference_model(fixture):
+    """bf16 autocast (BASELINE configs[3]: bf16 GEMMs, MSDA kernels on bf16 values with the index side in fp32) against
+    the float64 numbers of the unmodified reference: every loss term within 3 % (bf16 has 8 mantissa bits and the
+    decoder stacks 4-6 layers of them), the Hungarian assignment identical, gradient norms within 10 %."""
+    from dense_video_captioning_b200.pdvc import build
+    golden = load_golden("pdvc_" + fixture)
+    cfg = _cfg(golden)
+    model, criterion = build(cfg)
+    model.cuda().train()
+    criterion.cuda()
+    cases.fill_parameters(model)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out, loss = model(_batch(cfg, torch.float32, "cuda", golden), criterion)
+    wd = criterion.weight_dict
+    total = sum(loss[k].float() * wd[k] for k in loss if k in wd)
+    total.backward()
+    torch.cuda.synchronize()
+    want = dict(zip([str(n) for n in golden["loss_names"]], golden["loss_values"]))
+    for k, v in want.items():
+        assert abs(float(loss[k]) - v) <= 3e-2 * max(abs(v), 1.0), f"{k}: {float(loss[k])} vs {v}"
+    assert abs(float(total) - float(golden["total_loss"])) <= 3e-2 * float(golden["total_loss"])
+    q, t = out["matched_indices"][0]
+    assert q.tolist() == golden["matched_query"].tolist() and t.tolist() == golden["matched_target"].tolist()
+    norms = {cases.canonical_param_name(k): float(p.grad.float().norm()) for k, p in model.named_parameters() if p.grad is not None}
+    bad = [(n, norms[n], norm) for n, norm in zip([str(x) for x in golden["grad_names"]], golden["grad_norms"])
+           if abs(norms[n] - norm) > 0.1 * max(norm, 1e-2)]
+    assert not bad, bad[:8]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fixture", FIXTURES)
+def test_cuda_graph_step_matches_reference_model_fp32(fixture):
     """The two-graph step (capture + replay) against the golden numbers of the reference model."""
     from dense_video_captioning_b200.pdvc import build
     from dense_video_captioning_b200.pdvc.graphed import StagedStep
-    golden = load_golden("pdvc_anet_c3d")
+    golden = load_golden("pdvc_" + fixture)
     cfg = _cfg(golden)
     model, criterion = build(cfg)
     model.cuda().train()
     criterion.cuda()
     cases.fill_parameters(model)
     step = StagedStep(model, criterion, graphs=True)
-    dt = _batch(cfg, torch.float32, "cuda")
+    dt = _batch(cfg, torch.float32, "cuda", golden)
     want = dict(zip([str(n) for n in golden["loss_names"]], golden["loss_values"]))
     for rep in range(3):                      # rep 0 captures, reps 1-2 replay
         model.zero_grad(set_to_none=True)
