@@ -429,37 +429,86 @@ def reference_cuda_same_box(w, steps=20):
     shapes2 = torch.stack((torch.ones_like(w["shapes"]), w["shapes"]), -1).contiguous()
     value, gout = w["value"].float().contiguous(), w["grad_out"].float().contiguous()
 
-    def timed(fn):
+    def timed_n(fn, n):
         for _ in range(3):
             fn()
         torch.cuda.synchronize()
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
-        for _ in range(steps):
+        for _ in range(n):
             fn()
         e.record()
         torch.cuda.synchronize()
-        return s.elapsed_time(e) / steps
+        return s.elapsed_time(e) / n
+
+    def timed(fn):
+        return timed_n(fn, steps)
 
     r_fwd = timed(lambda: ref.ms_deform_attn_forward(value, shapes2, w["lsi"], loc, attn, 64))
     r_bwd = timed(lambda: ref.ms_deform_attn_backward(value, shapes2, w["lsi"], loc, attn, gout, 64))
-    from dense_video_captioning_b200.ops.functions import ms_deform_attn_func as fn_mod
     compat_dir = os.path.join(os.path.dirname(os.path.abspath(dvc.__file__)), "compat")
     if compat_dir not in sys.path:
         sys.path.insert(0, compat_dir)
     import MultiScaleDeformableAttention as ours   # the drop-in for the reference's extension module
-    prev = fn_mod.get_default_padding_mode()
-    fn_mod.set_default_padding_mode("zeros")
-    try:
-        o_fwd = timed(lambda: ours.ms_deform_attn_forward(value, shapes2, w["lsi"], loc, attn, 64))
-        o_bwd = timed(lambda: ours.ms_deform_attn_backward(value, shapes2, w["lsi"], loc, attn, gout, 64))
-    finally:
-        fn_mod.set_default_padding_mode(prev)
+    ours.padding_mode = "zeros"      # the module's default: what the extension it replaces does
+    o_fwd = timed(lambda: ours.ms_deform_attn_forward(value, shapes2, w["lsi"], loc, attn, 64))
+    o_bwd = timed(lambda: ours.ms_deform_attn_backward(value, shapes2, w["lsi"], loc, attn, gout, 64))
     q = N * Lq
-    return {"boundary": "unfused (sampling_locations + attention_weights in), ZEROS padding, fp32",
-            "reference_cuda": {"fwd_ms": r_fwd, "bwd_ms": r_bwd, "queries_per_s": q / ((r_fwd + r_bwd) * 1e-3)},
-            "ours_unfused": {"fwd_ms": o_fwd, "bwd_ms": o_bwd, "queries_per_s": q / ((o_fwd + o_bwd) * 1e-3)},
-            "speedup_fwd_bwd": (r_fwd + r_bwd) / (o_fwd + o_bwd)}
+    res = {"boundary": "unfused (sampling_locations + attention_weights in), ZEROS padding, fp32",
+           "reference_cuda": {"fwd_ms": r_fwd, "bwd_ms": r_bwd, "queries_per_s": q / ((r_fwd + r_bwd) * 1e-3)},
+           "ours_unfused": {"fwd_ms": o_fwd, "bwd_ms": o_bwd, "queries_per_s": q / ((o_fwd + o_bwd) * 1e-3)},
+           "speedup_fwd_bwd": (r_fwd + r_bwd) / (o_fwd + o_bwd)}
+    # configs[0] shapes (N = 1: where PDVC actually runs the op), microseconds per call, plain launches and CUDA-graph
+    # replay (20 calls per graph), the reference's kernels and ours on the same tensors
+    ours.ASSUME_1D = True        # PDVC's inputs (ms_deform_attn.py:114-117): no per-call inspection, capturable
+    small = {}
+    for kind in ("decoder", "encoder"):
+        ws = make_workload(1, 200, 8, 64, 4, 4, kind, w["value"].device, seed=3)
+        attn_s = torch.softmax(ws["logits"].flatten(-2), -1).view_as(ws["logits"]).contiguous()
+        xs = ws["ref"][:, :, None, :, None, 0] + ws["off"] / ws["shapes"].float()[None, None, None, :, None]
+        loc_s = torch.stack((xs, torch.full_like(xs, 0.5)), -1).contiguous()
+        sh2 = torch.stack((torch.ones_like(ws["shapes"]), ws["shapes"]), -1).contiguous()
+        val_s, gout_s = ws["value"].contiguous(), ws["grad_out"].contiguous()
+        row = {}
+        for who, mod in (("reference_cuda", ref), ("ours_unfused", ours)):
+            calls = {"fwd": lambda m=mod: m.ms_deform_attn_forward(val_s, sh2, ws["lsi"], loc_s, attn_s, 64),
+                     "bwd": lambda m=mod: m.ms_deform_attn_backward(val_s, sh2, ws["lsi"], loc_s, attn_s, gout_s, 64)}
+            for leg, fn in calls.items():
+                row[f"{who}_{leg}_us_plain"] = round(1e3 * timed_n(fn, 200), 2)
+                try:
+                    g = torch.cuda.CUDAGraph()
+                    side = torch.cuda.Stream()
+                    side.wait_stream(torch.cuda.current_stream())
+                    with torch.cuda.stream(side):
+                        fn()
+                    torch.cuda.current_stream().wait_stream(side)
+                    with torch.cuda.graph(g):
+                        for _ in range(20):
+                            fn()
+                    row[f"{who}_{leg}_us_graph"] = round(1e3 * timed_n(g.replay, 20) / 20, 2)
+                except Exception as ex:   # pragma: no cover
+                    row[f"{who}_{leg}_us_graph"] = f"capture failed: {ex!r}"[:120]
+        small[f"yc2_{kind}_N1"] = row
+    res["small_shapes_us"] = small
+    return res
+
+
+def sweep_max_point(peak, steps=5):
+    """BASELINE configs[4] maximum that fits one GPU: N=256, T0=2000 (S=Lq=3750), P=16, encoder geometry, fp32
+    (27.5 GB of algorithmic tensors per fwd+bwd).  Timed like the headline (CUDA events, device-resident inputs)."""
+    cfg = dict(N=256, T0=2000, M=8, D=64, L=4, P=16, kind="encoder")
+    w = make_workload(cfg["N"], cfg["T0"], cfg["M"], cfg["D"], cfg["L"], cfg["P"], cfg["kind"], "cuda", seed=17)
+    op = FusedOp(w)
+    total_ms, fwd_ms, bwd_ms = time_device(op, steps, 3, 1)
+    fb, bb = algorithmic_bytes(w, 4)
+    out = {"workload": f"N=256 T0=2000 S=Lq=3750 M=8 D=64 L=4 P=16 encoder fp32 (largest configs[4] point)",
+           "fwd_ms": fwd_ms, "bwd_ms": bwd_ms, "queries_per_s": cfg["N"] * w["Lq"] / ((fwd_ms + bwd_ms) * 1e-3),
+           "forward_frac": fb / (fwd_ms * 1e-3) / 1e9 / peak, "backward_frac": bb / (bwd_ms * 1e-3) / 1e9 / peak,
+           "fwd_bwd_frac": (fb + bb) / ((fwd_ms + bwd_ms) * 1e-3) / 1e9 / peak,
+           "algorithmic_bytes_fwd_bwd": fb + bb}
+    del op, w
+    torch.cuda.empty_cache()
+    return out
 
 
 def pdvc_train_leg(args, world, rank, device):
@@ -580,6 +629,14 @@ def run_ours(args, world, rank, local):
                         "traffic": traffic.get("forward_bytes_per_launch")},
             "fwd_bwd": {"achieved": (fb + bb) / ((fwd_ms + bwd_ms) * 1e-3) / 1e9,
                         "frac": (fb + bb) / ((fwd_ms + bwd_ms) * 1e-3) / 1e9 / peak}}
+    if world == 1 and not args.no_extra:
+        try:
+            del op
+            torch.cuda.empty_cache()
+            roof["sweep_max"] = sweep_max_point(peak)
+        except Exception as ex:   # must never cost the bench line
+            roof["sweep_max"] = {"error": repr(ex)[:200]}
+        op = None
     e2e_steps = max(3, min(args.steps, 20))
     e2e_ms, h2d, d2h = time_e2e(w, e2e_steps, 3, world)
     e2e_ms = max_over_ranks(e2e_ms, world, device)
@@ -596,7 +653,7 @@ def run_ours(args, world, rank, local):
         "gpu_launches": launches,
         "hbm_gbs_fwd_bwd": roof["fwd_bwd"]["achieved"],
     }
-    del op
+    op = None
     torch.cuda.empty_cache()
     if not args.no_pdvc:
         try:
@@ -634,6 +691,27 @@ def run_ours(args, world, rank, local):
                 line["extra"]["reference_cuda_same_box"] = reference_cuda_same_box(w)
             except Exception as ex:   # the comparison must never cost the bench line
                 line["extra"]["reference_cuda_same_box"] = {"error": repr(ex)}
+        # compact PDVC summary LAST (the driver keeps the tail of the line): videos/s per config, the exchange mode, and
+        # the weak-scaling efficiency against this box's N=1 run when one was recorded (the driver runs N=1,2,4,8 back to
+        # back on one box; the N=1 run leaves its figures in a scratch file)
+        cfgs = line.get("pdvc_train", {}).get("configs")
+        if cfgs:
+            vps = {k: round(v["videos_per_s"], 2) for k, v in cfgs.items()}
+            scratch = os.path.join(os.environ.get("TMPDIR", "/tmp"), "msda_bench_pdvc_n1.json")
+            eff = None
+            try:
+                if world == 1:
+                    with open(scratch, "w") as f:
+                        json.dump(vps, f)
+                else:
+                    with open(scratch) as f:
+                        n1 = json.load(f)
+                    eff = {k: round(vps[k] / (world * n1[k]), 4) for k in vps if n1.get(k)}
+            except Exception:
+                pass
+            line["pdvc_sync"] = args.pdvc_sync if world > 1 else "single process"
+            line["pdvc_weak_efficiency_vs_n1"] = eff
+            line["pdvc_videos_per_s"] = vps
         print(json.dumps(line), flush=True)
 
 
@@ -685,8 +763,9 @@ def main():
     ap.add_argument("--pdvc-steps", type=int, default=30)
     ap.add_argument("--pdvc-warmup", type=int, default=5)
     ap.add_argument("--pdvc-configs", default="", help="comma-separated subset of pdvc.CONFIGS (default: all)")
-    ap.add_argument("--pdvc-sync", default="flat", choices=["flat", "ddp"],
-                    help="gradient exchange at N>1: one flat all-reduce after backward, or torch DDP")
+    ap.add_argument("--pdvc-sync", default="overlap", choices=["overlap", "flat", "ddp"],
+                    help="gradient exchange at N>1: two buckets with the caption-head bucket reduced during the stage-1 "
+                         "backward graph (default), one flat all-reduce after backward, or torch DDP")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.sweep:

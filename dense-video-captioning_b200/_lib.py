@@ -17,6 +17,7 @@ CSRC = os.path.join(_HERE, "csrc")
 F32, BF16, F64 = 0, 1, 2
 PAD_BORDER, PAD_ZEROS = 0, 1
 FLAG_ASSUME_1D, FLAG_FORCE_GENERIC = 1, 2
+PATH_NONE, PATH_LEAN, PATH_TILE, PATH_FAST, PATH_GENERIC, PATH_SMALL = range(6)
 
 _vp, _i, _u, _sz, _ll = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint, ctypes.c_size_t, ctypes.c_longlong
 
@@ -26,6 +27,7 @@ SIGNATURES = {
     "msda_arch": (ctypes.c_char_p, []),
     "msda_error_string": (ctypes.c_char_p, [_i]),
     "msda_last_launch_count": (_i, []),
+    "msda_last_launch_path": (_i, []),
     "msda_backward_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "msda_ms_deform_attn_forward": (_i, [_vp] * 6 + [_i] * 7 + [_i, _i, _u, _vp]),
     "msda_ms_deform_attn_backward": (_i, [_vp] * 9 + [_vp, _sz] + [_i] * 7 + [_i, _i, _u, _vp]),

@@ -8,8 +8,14 @@ runs unmodified on top of the B200 library:
     ms_deform_attn_backward(value, spatial_shapes, level_start_index, sampling_loc, attn_weight, grad_output,
                             im2col_step) -> [grad_value, grad_sampling_loc, grad_attn_weight]
 
-Padding semantics follow dense_video_captioning_b200.ops.functions.get_default_padding_mode()
-('border' = the reference's PyTorch path; set 'zeros' to reproduce the reference CUDA kernel).
+Module-level switches:
+  padding_mode  'zeros' (default): what the extension this module replaces does (ms_deform_im2col_cuda.cuh:286-289);
+                'border': the reference's PyTorch path; None: follow functions.get_default_padding_mode().
+  ASSUME_1D     None (default): decide per call -- every level has H == 1 (cached per shapes tensor) and, under 'zeros',
+                every sampling_loc[..., 1] == 0.5, which costs ONE blocking device->host read per call (the row weight
+                depends on y there), so such calls are not CUDA-graph capturable;
+                True: the caller guarantees both (PDVC always: ms_deform_attn.py:114-117) -- no host read, capturable;
+                False: always take the shape-generic 2-D kernels.
 """
 import os
 import sys
@@ -23,6 +29,9 @@ if _root not in sys.path:
 from dense_video_captioning_b200 import _lib  # noqa: E402
 from dense_video_captioning_b200.ops.functions import ms_deform_attn_func as _f  # noqa: E402
 
+padding_mode = "zeros"
+ASSUME_1D = None
+
 
 def _common(value, spatial_shapes, level_start_index, sampling_loc, attn_weight):
     _f._check_cuda_contig(value=value, spatial_shapes=spatial_shapes, level_start_index=level_start_index,
@@ -31,8 +40,9 @@ def _common(value, spatial_shapes, level_start_index, sampling_loc, attn_weight)
     _f._require(sampling_loc.dtype == value.dtype and attn_weight.dtype == value.dtype, "dtype mismatch")
     N, S, M, D = value.shape
     _, Lq, _, L, P, _ = sampling_loc.shape
-    pad = _f._pad_code(None)
-    flags = _lib.FLAG_ASSUME_1D if _f._auto_1d(spatial_shapes, None, sampling_loc, pad) else 0
+    pad = _f._pad_code(padding_mode)
+    one_d = _f._auto_1d(spatial_shapes, None, sampling_loc, pad) if ASSUME_1D is None else bool(ASSUME_1D)
+    flags = _lib.FLAG_ASSUME_1D if one_d else 0
     return N, S, M, D, L, Lq, P, _f._DTYPES[value.dtype], pad, flags
 
 

@@ -20,21 +20,50 @@ using namespace msda;
 
 namespace {
 
+// Diagnostics only (msda_last_launch_count / msda_last_launch_path): per-thread, reset by every entry point.
 thread_local int g_launches = 0;
+thread_local int g_path = MSDA_PATH_NONE;
 
-constexpr int kNumSMs = 148;   // B200; grids are sized in multiples of it
+// Tuning knobs are compiled in only with -DMSDA_TUNING (development builds, tools/); the shipped library reads no
+// environment variable.
+inline int env_int(const char *name, int dflt)
+{
+#ifdef MSDA_TUNING
+    const char *e = getenv(name);
+    return e ? atoi(e) : dflt;
+#else
+    (void)name;
+    return dflt;
+#endif
+}
+
+// SM count of the current device (grids are sized in multiples of it): queried once per device ordinal, an
+// immutable device property.
+inline int num_sms()
+{
+    static int cache[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    int v = cache[dev];
+    if (v == 0) {
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+        cache[dev] = v;
+    }
+    return v;
+}
 
 inline int head_major_env()
 {
-    static const int v = [] { const char *e = getenv("MSDA_HEAD_MAJOR"); return e ? atoi(e) : 1; }();
+    static const int v = env_int("MSDA_HEAD_MAJOR", 1);
     return v;
 }
 
 inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-inline int check_launch()
+inline int check_launch(int path = 0)
 {
     ++g_launches;
+    if (path) g_path = path;
     const cudaError_t e = cudaGetLastError();
     return (int)e;
 }
@@ -76,7 +105,7 @@ void fast_grid(int total_units, int lpg, int &grid, int &units_per_cta)
     const int g = 32 / lpg;
     const long long per_iter = (long long)kFastWarps * g;   // units one CTA covers per loop trip
     long long ctas = (total_units + per_iter - 1) / per_iter;
-    const long long cap = (long long)kNumSMs * 16;          // <= 16 resident 128-thread CTAs per SM
+    const long long cap = (long long)num_sms() * 16;          // <= 16 resident 128-thread CTAs per SM
     if (ctas > cap) ctas = cap;
     long long upc = (total_units + ctas - 1) / ctas;
     upc = (upc + per_iter - 1) / per_iter * per_iter;
@@ -95,7 +124,7 @@ template <typename VT, bool FUSED> int launch_fast_fwd(const FastArgs &a, int lp
         case 16: msda_fwd_fast_kernel<VT, 16, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
         default: msda_fwd_fast_kernel<VT, 32, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
     }
-    return check_launch();
+    return check_launch(MSDA_PATH_FAST);
 #endif
 }
 
@@ -110,17 +139,11 @@ template <typename VT, bool FUSED> int launch_fast_bwd(const FastArgs &a, int lp
         case 16: msda_bwd_fast_kernel<VT, 16, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
         default: msda_bwd_fast_kernel<VT, 32, FUSED><<<grid, kFastThreads, 0, st>>>(a); break;
     }
-    return check_launch();
+    return check_launch(MSDA_PATH_FAST);
 #endif
 }
 
 // ---- chunked ("tile") kernels: planning ----------------------------------------------------------
-
-inline int env_int(const char *name, int dflt)
-{
-    const char *e = getenv(name);
-    return e ? atoi(e) : dflt;
-}
 
 struct TilePlan {
     bool ok;
@@ -154,7 +177,8 @@ TilePlan tile_plan(const Dims &d, int dtype, bool backward)
     int Q = 1024 / p.LPpad;
     Q = Q > 64 ? 64 : (Q < 4 ? 4 : Q);
     // small problems: more, smaller chunks so that every SM gets a CTA
-    while (Q > 8 && (long long)d.N * d.M * ((d.Lq + Q - 1) / Q) < 2 * kNumSMs) Q >>= 1;
+    const int sms = num_sms();
+    while (Q > 8 && (long long)d.N * d.M * ((d.Lq + Q - 1) / Q) < 2 * sms) Q >>= 1;
     if (q_env > 0) Q = q_env;
     if (Q > d.Lq) Q = d.Lq;
     if (Q * p.LPpad > kTileMaxSamples) return p;
@@ -213,7 +237,7 @@ int launch_tile_inst(const TileArgs &a, int grid, size_t smem, cudaStream_t st)
         if (int e = allow_big_smem(msda_fwd_tile_kernel<VT, LPG, LPA, FUSED>, done)) return e;
         msda_fwd_tile_kernel<VT, LPG, LPA, FUSED><<<grid, kTileThreads, smem, st>>>(a);
     }
-    return check_launch();
+    return check_launch(MSDA_PATH_TILE);
 }
 
 template <typename VT, bool FUSED, bool BWD>
@@ -272,7 +296,8 @@ LeanPlan lean_plan(const Dims &d, int dtype, bool backward)
     const int upp = kLeanWarps * (32 / p.lpa);
     int passes = kLeanPasses / p.spl;
     // small problems: fewer queries per CTA so that every SM gets work
-    while (passes > 1 && (long long)d.N * d.M * ((d.Lq + upp * passes - 1) / (upp * passes)) < 2 * kNumSMs) passes >>= 1;
+    const int sms = num_sms();
+    while (passes > 1 && (long long)d.N * d.M * ((d.Lq + upp * passes - 1) / (upp * passes)) < 2 * sms) passes >>= 1;
     if (passes_env > 0 && passes_env <= kLeanPasses / p.spl) passes = passes_env;
     p.Q = upp * passes;
     p.chunks = (d.Lq + p.Q - 1) / p.Q;
@@ -333,7 +358,7 @@ int launch_lean_inst(const TileArgs &a, const LeanPlan &p, cudaStream_t st)
         if (int e = allow_big_smem(msda_fwd_lean_kernel<VT, LPG, NCH, LPA, FUSED, SPL>, done)) return e;
         msda_fwd_lean_kernel<VT, LPG, NCH, LPA, FUSED, SPL><<<grid, kLeanThreads, p.smem, st>>>(a);
     }
-    return check_launch();
+    return check_launch(MSDA_PATH_LEAN);
 }
 
 template <typename VT, bool FUSED, bool BWD> int launch_lean_shape(const TileArgs &a, const LeanPlan &p, cudaStream_t st)
@@ -362,7 +387,7 @@ template <bool FUSED, bool BWD> int launch_lean(const TileArgs &a, const LeanPla
 int generic_grid(long long total)
 {
     long long blocks = (total + 255) / 256;
-    const long long cap = (long long)kNumSMs * 32;
+    const long long cap = (long long)num_sms() * 32;
     return (int)(blocks > cap ? cap : blocks);
 }
 
@@ -372,7 +397,7 @@ template <bool SAMPLER> int launch_generic_fwd(const GenericArgs &a, int dtype, 
     if (dtype == MSDA_F32) msda_fwd_generic_kernel<float, SAMPLER><<<grid, 256, 0, st>>>(a);
     else if (dtype == MSDA_F64) msda_fwd_generic_kernel<double, SAMPLER><<<grid, 256, 0, st>>>(a);
     else msda_fwd_generic_kernel<__nv_bfloat16, SAMPLER><<<grid, 256, 0, st>>>(a);
-    return check_launch();
+    return check_launch(MSDA_PATH_GENERIC);
 }
 
 template <bool SAMPLER> int launch_generic_bwd(const GenericArgs &a, int dtype, cudaStream_t st)
@@ -381,7 +406,7 @@ template <bool SAMPLER> int launch_generic_bwd(const GenericArgs &a, int dtype, 
     if (dtype == MSDA_F32) msda_bwd_generic_kernel<float, SAMPLER><<<grid, 256, 0, st>>>(a);
     else if (dtype == MSDA_F64) msda_bwd_generic_kernel<double, SAMPLER><<<grid, 256, 0, st>>>(a);
     else msda_bwd_generic_kernel<__nv_bfloat16, SAMPLER><<<grid, 256, 0, st>>>(a);
-    return check_launch();
+    return check_launch(MSDA_PATH_GENERIC);
 }
 
 int memset_async(void *p, size_t bytes, cudaStream_t st)
@@ -396,7 +421,8 @@ int finish_bf16(const float *acc, void *grad_value, long long n, cudaStream_t st
     if (n % 8 == 0) {
         const long long n8 = n / 8;
         long long blocks = (n8 + 255) / 256;
-        if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+        const int cap = num_sms() * 16;
+        if (blocks > cap) blocks = cap;
         msda_cvt_f32_to_bf16_kernel<<<(int)blocks, 256, 0, st>>>(acc, static_cast<__nv_bfloat16 *>(grad_value), n8);
     } else {
         msda_cvt_f32_to_bf16_scalar_kernel<<<generic_grid(n), 256, 0, st>>>(acc, static_cast<__nv_bfloat16 *>(grad_value), n);
@@ -411,6 +437,7 @@ extern "C" {
 int msda_version(void) { return MSDA_VERSION; }
 const char *msda_arch(void) { return "sm_100a"; }
 int msda_last_launch_count(void) { return g_launches; }
+int msda_last_launch_path(void) { return g_path; }
 #ifdef MSDA_PHASE_TIMING
 int msda_dev_phase_clocks(unsigned long long *out32, int reset)
 {
@@ -446,7 +473,7 @@ int msda_ms_deform_attn_forward(const void *value, const int64_t *spatial_shapes
                                 const void *sampling_loc, const void *attn_weight, void *output, int N, int S, int M,
                                 int D, int L, int Lq, int P, int dtype, int pad_mode, unsigned flags, void *stream)
 {
-    g_launches = 0;
+    g_launches = 0; g_path = MSDA_PATH_NONE;
     const Dims d{N, S, M, D, L, Lq, P};
     if (int e = check_dims(d, dtype, pad_mode)) return e;
     if (!value || !spatial_shapes || !level_start_index || !sampling_loc || !attn_weight || !output) return MSDA_ERR_NULL;
@@ -498,7 +525,7 @@ int msda_ms_deform_attn_backward(const void *value, const int64_t *spatial_shape
                                  size_t workspace_bytes, int N, int S, int M, int D, int L, int Lq, int P, int dtype,
                                  int pad_mode, unsigned flags, void *stream)
 {
-    g_launches = 0;
+    g_launches = 0; g_path = MSDA_PATH_NONE;
     const Dims d{N, S, M, D, L, Lq, P};
     if (int e = check_dims(d, dtype, pad_mode)) return e;
     if (!value || !spatial_shapes || !level_start_index || !sampling_loc || !attn_weight || !grad_output || !grad_value ||
@@ -570,7 +597,7 @@ int msda_fused_forward(const void *value, const int64_t *temporal_shapes, const 
                        unsigned flags, void *stream)
 {
     (void)flags;
-    g_launches = 0;
+    g_launches = 0; g_path = MSDA_PATH_NONE;
     const Dims d{N, S, M, D, L, Lq, P};
     if (int e = check_dims(d, dtype, pad_mode)) return e;
     if (R != 1 && R != 2) return MSDA_ERR_SHAPE;
@@ -617,7 +644,7 @@ int msda_fused_backward(const void *value, const int64_t *temporal_shapes, const
                         void *stream)
 {
     (void)flags;
-    g_launches = 0;
+    g_launches = 0; g_path = MSDA_PATH_NONE;
     const Dims d{N, S, M, D, L, Lq, P};
     if (int e = check_dims(d, dtype, pad_mode)) return e;
     if (R != 1 && R != 2) return MSDA_ERR_SHAPE;
@@ -678,7 +705,7 @@ int msda_sample_forward(const void *value, const int64_t *spatial_shapes, const 
                         const void *sampling_loc, void *samples, int N, int S, int M, int D, int L, int Lq, int P,
                         int dtype, int pad_mode, unsigned flags, void *stream)
 {
-    g_launches = 0;
+    g_launches = 0; g_path = MSDA_PATH_NONE;
     const Dims d{N, S, M, D, L, Lq, P};
     if (int e = check_dims(d, dtype, pad_mode)) return e;
     if (!value || !spatial_shapes || !level_start_index || !sampling_loc || !samples) return MSDA_ERR_NULL;
@@ -696,7 +723,7 @@ int msda_cap_sample_forward(const void *value, const int64_t *temporal_shapes, c
                             int M, int D, int L, int Lq, int P, int R, int dtype, int pad_mode, unsigned flags, void *stream)
 {
     (void)flags;
-    g_launches = 0;
+    g_launches = 0; g_path = MSDA_PATH_NONE;
     const Dims d{N, S, M, D, L, Lq, P};
     if (int e = check_dims(d, dtype, pad_mode)) return e;
     if (R != 1 && R != 2) return MSDA_ERR_SHAPE;
@@ -710,7 +737,8 @@ int msda_cap_sample_forward(const void *value, const int64_t *temporal_shapes, c
     a.N = N; a.S = S; a.M = M; a.D = D; a.L = L; a.Lq = Lq; a.P = P; a.R = R; a.pad_mode = pad_mode;
     a.total = (long long)N * Lq * M * L * P * (D / ch);
     long long blocks = (a.total + 255) / 256;
-    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    const int cap = num_sms() * 8;
+    if (blocks > cap) blocks = cap;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (dtype == MSDA_F32) msda_cap_fwd_kernel<float><<<(int)blocks, 256, 0, st>>>(a);
     else msda_cap_fwd_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, st>>>(a);
@@ -727,7 +755,7 @@ static int attend_check(int BM, int M, int K, int D, int A)
 int msda_cap_attend_forward_f32(const float *samples, const float *hproj, const float *alpha, const float *alpha_bias,
                                 float *attended, float *weight, int BM, int M, int K, int D, int A, void *stream)
 {
-    g_launches = 0;
+    g_launches = 0; g_path = MSDA_PATH_NONE;
     if (int e = attend_check(BM, M, K, D, A)) return e;
     if (!samples || !hproj || !alpha || !alpha_bias || !attended || !weight) return MSDA_ERR_NULL;
     AttendArgs a{};
@@ -742,7 +770,7 @@ int msda_cap_attend_backward_f32(const float *samples, const float *hproj, const
                                  const float *grad_attended, float *grad_samples, float *grad_hproj, float *grad_alpha,
                                  int BM, int M, int K, int D, int A, void *stream)
 {
-    g_launches = 0;
+    g_launches = 0; g_path = MSDA_PATH_NONE;
     if (int e = attend_check(BM, M, K, D, A)) return e;
     if (!samples || !hproj || !alpha || !weight || !grad_attended || !grad_samples || !grad_hproj || !grad_alpha) return MSDA_ERR_NULL;
     AttendArgs a{};
@@ -759,7 +787,7 @@ int msda_cap_attend_backward_f32(const float *samples, const float *hproj, const
 int msda_skinny_linear_f32(const float *x, const float *weight, const float *bias, float *y, int M, int N, int K,
                            void *stream)
 {
-    g_launches = 0;
+    g_launches = 0; g_path = MSDA_PATH_NONE;
     if (M <= 0 || N <= 0 || K <= 0 || (K & 3)) return MSDA_ERR_SHAPE;
     if (!x || !weight || !y) return MSDA_ERR_NULL;
     if (!aligned16(x) || !aligned16(weight)) return MSDA_ERR_ALIGN;
@@ -768,7 +796,8 @@ int msda_skinny_linear_f32(const float *x, const float *weight, const float *bia
     const int mtiles = (M + rows - 1) / rows;
     // K split: every lane of every slice gets a float4, and no more than ~4 CTAs per SM (each CTA should still have work)
     int ks = K4 >= 256 ? 8 : K4 >= 128 ? 4 : K4 >= 64 ? 2 : 1;
-    while (ks > 1 && (long long)((N + (kSkinnyWarps / ks) * kSkinnyNW - 1) / ((kSkinnyWarps / ks) * kSkinnyNW)) * mtiles > 4 * kNumSMs)
+    const int sms = num_sms();
+    while (ks > 1 && (long long)((N + (kSkinnyWarps / ks) * kSkinnyNW - 1) / ((kSkinnyWarps / ks) * kSkinnyNW)) * mtiles > 4 * sms)
         ks >>= 1;
     const int per_cta = (kSkinnyWarps / ks) * kSkinnyNW;
     const dim3 grid((N + per_cta - 1) / per_cta, mtiles);
@@ -796,7 +825,7 @@ int msda_skinny_linear_f32(const float *x, const float *weight, const float *bia
 int msda_lstm_cell_forward_f32(const float *pre, long long pre_row_stride, const float *rec, const float *c_prev,
                                float *c, float *h, float *act, int B, int H, void *stream)
 {
-    g_launches = 0;
+    g_launches = 0; g_path = MSDA_PATH_NONE;
     if (B <= 0 || H <= 0 || pre_row_stride < 4LL * H) return MSDA_ERR_SHAPE;
     if (!pre || !rec || !c_prev || !c || !h || !act) return MSDA_ERR_NULL;
     msda_lstm_cell_fwd_kernel<<<(B * H + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
@@ -807,7 +836,7 @@ int msda_lstm_cell_forward_f32(const float *pre, long long pre_row_stride, const
 int msda_lstm_cell_backward_f32(const float *grad_h, const float *grad_c, const float *act, const float *c,
                                 const float *c_prev, float *grad_gates, float *grad_c_prev, int B, int H, void *stream)
 {
-    g_launches = 0;
+    g_launches = 0; g_path = MSDA_PATH_NONE;
     if (B <= 0 || H <= 0) return MSDA_ERR_SHAPE;
     if (!act || !c || !c_prev || !grad_gates || !grad_c_prev) return MSDA_ERR_NULL;
     msda_lstm_cell_bwd_kernel<<<(B * H + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
@@ -822,7 +851,7 @@ int msda_cap_sample_backward(const void *value, const int64_t *temporal_shapes, 
                              int R, int dtype, int pad_mode, unsigned flags, void *stream)
 {
     (void)flags;
-    g_launches = 0;
+    g_launches = 0; g_path = MSDA_PATH_NONE;
     const Dims d{N, S, M, D, L, Lq, P};
     if (int e = check_dims(d, dtype, pad_mode)) return e;
     if (R != 1 && R != 2) return MSDA_ERR_SHAPE;
@@ -850,7 +879,8 @@ int msda_cap_sample_backward(const void *value, const int64_t *temporal_shapes, 
     a.total = ns * (D / ch);
     // grid-stride with whole-warp liveness: the grid covers `total` in full rounds of the same stride
     long long blocks = (a.total + 255) / 256;
-    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    const int cap = num_sms() * 8;
+    if (blocks > cap) blocks = cap;
     if (dtype == MSDA_F32) msda_cap_bwd_kernel<float><<<(int)blocks, 256, 0, st>>>(a);
     else msda_cap_bwd_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, st>>>(a);
     if (int rc = check_launch()) return rc;
@@ -863,7 +893,7 @@ int msda_sample_backward(const void *value, const int64_t *spatial_shapes, const
                          void *workspace, size_t workspace_bytes, int N, int S, int M, int D, int L, int Lq, int P,
                          int dtype, int pad_mode, unsigned flags, void *stream)
 {
-    g_launches = 0;
+    g_launches = 0; g_path = MSDA_PATH_NONE;
     const Dims d{N, S, M, D, L, Lq, P};
     if (int e = check_dims(d, dtype, pad_mode)) return e;
     if (!value || !spatial_shapes || !level_start_index || !sampling_loc || !grad_samples || !grad_value || !grad_sampling_loc)

@@ -87,6 +87,32 @@ def _shapes_are_1d(shapes):
     return flag
 
 
+_layout_cache = {}
+
+
+def _check_level_layout(shapes, lsi, S):
+    """The reference asserts sum_l H_l*W_l == Len_in (ms_deform_attn.py:89); the kernels index value rows as
+    level_start_index[l] + i and tile self-attention by sum(T_l) == Lq, so an inconsistent pair of level tensors
+    would read out of bounds or leave output rows unwritten.  Checked on the host once per (shapes, lsi) tensor pair
+    (keyed on identity + version: one small device->host read the first time a pair is seen, none afterwards; skipped
+    while a CUDA graph is being captured -- the warm-up runs before a capture have already seen the tensors)."""
+    key = (id(shapes), id(lsi), int(S))
+    hit = _layout_cache.get(key)
+    if hit is not None and hit[0]() is shapes and hit[1]() is lsi and hit[2] == (shapes._version, lsi._version):
+        return
+    if torch.cuda.is_current_stream_capturing():
+        return
+    sz = (shapes if shapes.dim() == 1 else shapes[:, 0] * shapes[:, 1]).cpu()
+    want = torch.cat((sz.new_zeros(1), sz.cumsum(0)[:-1]))
+    _require(int(sz.sum()) == int(S), f"spatial_shapes cover {int(sz.sum())} rows but value has {int(S)} "
+                                      "(the reference asserts their equality, ms_deform_attn.py:89)")
+    _require(bool((sz > 0).all()), "every level must have at least one row")
+    _require(torch.equal(lsi.cpu(), want), "level_start_index is not the exclusive prefix sum of the level sizes")
+    if len(_layout_cache) > 256:
+        _layout_cache.clear()
+    _layout_cache[key] = (weakref.ref(shapes), weakref.ref(lsi), (shapes._version, lsi._version))
+
+
 def _auto_1d(shapes, is1d, loc, pad):
     """Decide whether the 1-D temporal kernels may take a call whose caller did not say.
     H == 1 everywhere is enough under BORDER (the clamped y has no effect at all); under ZEROS the
@@ -143,6 +169,7 @@ class MSDeformAttnFunction(Function):
         _require(M2 == M and sampling_locations.shape[0] == N, "sampling_locations does not match value")
         _require(tuple(attention_weights.shape) == (N, Lq, M, L, P), "attention_weights must be (N, Lq, M, L, P)")
         _require(shapes.shape[0] == L and value_level_start_index.numel() == L, "level tensors do not match L")
+        _check_level_layout(value_spatial_shapes, value_level_start_index, S)
         pad = _pad_code(padding_mode)
         if assume_1d is None:
             assume_1d = _auto_1d(shapes, is1d, sampling_locations, pad)
@@ -222,6 +249,7 @@ class MSDeformAttnFusedFunction(Function):
         if R not in (1, 2):
             raise ValueError(f"Last dim of reference_points must be 1 or 2, but get {R} instead.")
         _require(temporal_shapes.numel() == L and level_start_index.numel() == L, "level tensors do not match L")
+        _check_level_layout(temporal_shapes, level_start_index, S)
         pad = _pad_code(padding_mode)
         out = torch.empty((N, Lq, M * D), dtype=value.dtype, device=value.device)
         with torch.cuda.device(value.device):
@@ -275,6 +303,7 @@ class MSDeformSampleFunction(Function):
         shapes, is1d = _normalise_shapes(value_spatial_shapes)
         N, S, M, D = value.shape
         _, Lq, _, L, P, _ = sampling_locations.shape
+        _check_level_layout(value_spatial_shapes, value_level_start_index, S)
         pad = _pad_code(padding_mode)
         if assume_1d is None:
             assume_1d = _auto_1d(shapes, is1d, sampling_locations, pad)
@@ -345,6 +374,7 @@ class MSDeformCapSampleFunction(Function):
         _require(tuple(reference_points.shape) == (N, Lq, L, R), "reference_points must be (N, Lq, L, R)")
         if R not in (1, 2):
             raise ValueError(f"Last dim of reference_points must be 1 or 2, but get {R} instead.")
+        _check_level_layout(temporal_shapes, level_start_index, S)
         pad = _pad_code(padding_mode)
         out = torch.empty((N, Lq, M, L * P, D), dtype=value.dtype, device=value.device)
         with torch.cuda.device(value.device):

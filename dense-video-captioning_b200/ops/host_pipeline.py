@@ -109,4 +109,9 @@ class HostPipelinedFusedMSDA:
                     h[lo:hi].copy_(d, non_blocking=True)
         caller.wait_stream(self.main)
         caller.wait_stream(self.copy_out)
+        # the returned tensors are HOST buffers filled by asynchronous copies: block the host until they have landed
+        # (stream order alone only protects later GPU work)
+        done = torch.cuda.Event()
+        done.record(self.copy_out)
+        done.synchronize()
         return tuple(outs)

@@ -14,6 +14,10 @@ class MSDeformAttnCap(_MSDeformFrontEnd):
 
     def __init__(self, d_model=256, n_levels=4, n_heads=8, n_points=4):
         super().__init__(d_model, n_levels, n_heads, n_points)
+        # The reference's caption sampler ALWAYS samples with border padding (its grid_sample route), also on CUDA
+        # (ms_deform_attn_for_caption.py:120-121): functions.set_default_padding_mode('zeros') -- the switch for
+        # checkpoints trained with the reference CUDA extension -- must not reach it.
+        self.padding_mode = "border"
 
     def forward(self, query, reference_points, input_flatten, input_spatial_shapes, input_level_start_index,
                 input_padding_mask=None, projected_value=None, sampling_offsets=None):

@@ -10,9 +10,11 @@ Hungarian assignment (scipy, pdvc/matcher.py:115-117).  So the step is split the
 
 Each stage is captured once per shape key by `graph_module` below (forward graph + backward graph; the MSDeformAttn /
 MSDeformAttnCap CUDA kernels are captured like any other launch: the C ABI does no allocation and no
-synchronisation).  `total.backward()` replays stage 2's backward graph, then stage 1's; parameter gradients leave the
-graphs through autograd's AccumulateGrad, so DDP's bucketed NCCL all-reduce hooks fire as usual and overlap stage 1's
-backward with the all-reduce of the caption-head gradients.
+synchronisation).  `total.backward()` replays stage 2's backward graph, then stage 1's.  Parameter gradients leave the
+graphs either through autograd's AccumulateGrad (default; what torch DDP's hooks need) or -- `grad_sinks`, used by
+Trainer(sync="overlap") -- through multi-tensor copies captured at the end of each backward graph that write them
+straight into the trainer's flat gradient buckets; a stage's `after_backward` callback then starts that bucket's NCCL
+all-reduce, so the caption-head bucket (stage 2) is reduced while stage 1's backward graph replays.
 
 Shape key of stage 2: (events, matched pairs, word steps per layer) -- a new key is captured on first use and cached.
 `graphs=False` runs the same two stages eagerly (used by the CPU tests and as the reference for the graph tests).
@@ -36,12 +38,17 @@ def pyramid_lengths(t0, n_levels):
     return out
 
 
-def graph_module(module, sample_args, warmup=3, autocast=None):
+def graph_module(module, sample_args, warmup=3, autocast=None, grad_sinks=None):
     """Capture `module(*sample_args)` as a forward CUDA graph and its autograd backward as a second graph; return a
     callable with the same signature whose result is differentiable w.r.t. the tensor arguments and the module's
     trainable parameters (the scheme of torch.cuda.make_graphed_callables, written out so that the capture runs in
     `thread_local` error mode -- NCCL's watchdog thread may poll events while a rank is capturing -- and outputs that
-    carry no gradient are marked non-differentiable)."""
+    carry no gradient are marked non-differentiable).
+
+    grad_sinks: {id(parameter): tensor view} -- the backward graph ends with multi-tensor copies of those parameters'
+    gradients into the given views (zero-fill where a parameter got none) and autograd receives no gradient for them:
+    the caller owns `.grad` (views of a flat bucket).  The returned callable's `after_backward` attribute, when set, is
+    called right after the backward graph has been enqueued."""
     params = tuple(p for p in module.parameters() if p.requires_grad)
     surface = tuple(sample_args) + params
     diff_inputs = tuple(t for t in surface if t.requires_grad)
@@ -81,6 +88,21 @@ def graph_module(module, sample_args, warmup=3, autocast=None):
         static_grad_outs = tuple(torch.zeros_like(o) if o.requires_grad else None for o in static_outs)
         with torch.cuda.graph(bwd_graph, pool=pool, capture_error_mode="thread_local"):
             grads = backward_of(static_outs, static_grad_outs)
+            if grad_sinks:
+                grads = list(grads)
+                src, dst = [], []
+                for i, t in enumerate(diff_inputs):
+                    sink = grad_sinks.get(id(t))
+                    if sink is None:
+                        continue
+                    if grads[i] is None:
+                        sink.zero_()
+                    else:
+                        src.append(grads[i].reshape(sink.shape).to(sink.dtype))
+                        dst.append(sink)
+                    grads[i] = None                  # nothing for AccumulateGrad: the sink IS the parameter's .grad
+                if src:
+                    torch._foreach_copy_(dst, src)
     finally:
         if gc_was_enabled:
             gc.enable()
@@ -106,12 +128,15 @@ def graph_module(module, sample_args, warmup=3, autocast=None):
                 if static is not None and new is not None and static.data_ptr() != new.data_ptr():
                     static.copy_(new)
             bwd_graph.replay()
+            if call.after_backward is not None:
+                call.after_backward()
             return tuple(g.detach() if g is not None else None for g in static_grad_inputs)
 
     def call(*user_args):
         return Graphed.apply(*(tuple(user_args) + params))
 
     call.graphs = (fwd_graph, bwd_graph)
+    call.after_backward = None
     # the parameters' AccumulateGrad nodes were created on the capture stream and are kept alive by the captured autograd
     # graph; later backwards run on the caller's stream -- intended, autograd inserts the stream wait
     quiet = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
@@ -216,7 +241,8 @@ class LossStage(nn.Module):
 
         shared = (self.batch_layers and len(set(self.n_steps)) == 1 and n_pred > 1
                   and all(head is self.caption_head[0] for head in self.caption_head)
-                  and self.caption_head[0].core.n_levels == len(self.level_lengths))
+                  and self.caption_head[0].core.n_levels == len(self.level_lengths)
+                  and inter_references.shape[-1] == 2)     # with_box_refine=0 keeps 1-coordinate references: per-layer path
         if shared:
             # One caption head shared by all decoder layers (opts.py:148, the default): the layers' matched pairs are
             # independent sentences for the SAME weights, so they are decoded as ONE batch of n_pred * pairs sentences --
@@ -278,6 +304,9 @@ class StagedStep(nn.Module):
         self.graphs = graphs
         self.amp = amp
         self.max_graphs = max_graphs      # stage-2 graphs kept (one per shape key, least recently used dropped first)
+        # Trainer(sync="overlap"): {id(param): flat-bucket view} and one callback per stage (see graph_module)
+        self.__dict__["grad_sinks"] = None
+        self.__dict__["after_backward"] = {1: None, 2: None}
         self.stage1 = FeatureStage(model, criterion.matcher)
         self.__dict__["_stage1"] = {}
         self.__dict__["_stage2"] = {}
@@ -313,8 +342,15 @@ class StagedStep(nn.Module):
             return (total / torch.distributed.get_world_size()).clamp(min=1)[0]
         return torch.full((), max(float(n_gt), 1.0), device=device)
 
-    def _graph(self, module, args):
-        return graph_module(module, args, autocast=torch.bfloat16 if self.amp else None)
+    def _graph(self, module, args, stage):
+        call = graph_module(module, args, autocast=torch.bfloat16 if self.amp else None, grad_sinks=self.grad_sinks)
+        call.after_backward = self.after_backward[stage]
+        return call
+
+    def stage2_parameters(self):
+        """Parameters only stage 2 (losses + caption loops) reaches: their gradients are final when stage 2's backward
+        ends, i.e. before stage 1's backward starts."""
+        return [p for p in self.model.caption_head.parameters() if p.requires_grad]
 
     def _cached(self, cache, key, make):
         """Least-recently-used cache of captured stages, at most max_graphs per stage."""
@@ -336,7 +372,7 @@ class StagedStep(nn.Module):
         stage1 = self.stage1
         if use_graphs:      # the matching costs are part of stage 1, so its graph depends on the event count too
             key1 = (int(vf.shape[1]), int(target['boxes'].shape[0]))
-            stage1 = self._cached(self._stage1, key1, lambda: self._graph(self.stage1, tuple(a.detach().clone() for a in args1)))
+            stage1 = self._cached(self._stage1, key1, lambda: self._graph(self.stage1, tuple(a.detach().clone() for a in args1), 1))
         # the event count is host data: its all-reduce (criterion.py:169-171) is issued before stage 1 and has long
         # finished when stage 2 reads it, instead of making the ranks meet in the middle of the step
         num_boxes = self._num_boxes(int(target['boxes'].shape[0]), vf.device)
@@ -359,7 +395,7 @@ class StagedStep(nn.Module):
                 # replay wrapper finds identical addresses and skips its input copies; everything else is cloned
                 sample = tuple((a.detach() if (ALIAS_STAGE_INPUTS and i < 9) else a.detach().clone()).requires_grad_(a.requires_grad)
                                for i, a in enumerate(args2))
-                stage2 = self._graph(stage2, sample)
+                stage2 = self._graph(stage2, sample, 2)
             return stage2
 
         total, terms = self._cached(self._stage2, key, make_stage2)(*args2)

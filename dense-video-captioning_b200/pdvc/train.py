@@ -3,9 +3,15 @@
 What the reference does per iteration (train.py:163-194): move the batch to the device, forward with the criterion,
 weighted loss sum, backward, clip_grad_norm_(100), Adam step -- batch size 1 video, with a `cuda.synchronize()` before
 and after every iteration.  Same step here, minus the two forced synchronisations, with the inputs copied from pinned
-host memory each step, and -- new, the reference never wraps PDVC in DDP (SURVEY finding 0.8) -- one process per GPU with
-`DistributedDataParallel` (NCCL all-reduce of the gradients, bucketed and overlapped with backward).  Ranks own
-disjoint videos (video i of step s goes to rank i); the learning rate is not rescaled (the reference has no rule).
+host memory each step, and -- new, the reference never wraps PDVC in DDP (SURVEY finding 0.8) -- one process per GPU
+with an NCCL all-reduce (mean) of the gradients.  Three exchange modes (`Trainer(sync=...)`):
+  'overlap' (default)  two flat buckets; the caption-head bucket is reduced on a side stream WHILE the stage-1 backward
+                       graph replays, the rest right after it; gradients reach the buckets through copies captured in
+                       the backward graphs (no per-step concatenation, no AccumulateGrad traffic);
+  'flat'               one concatenation + one all-reduce after both backward graphs (no overlap; round-1 default);
+  'ddp'                torch DistributedDataParallel (bucket hooks on AccumulateGrad).
+Ranks own disjoint videos (video i of step s goes to rank i); the learning rate is not rescaled (the reference has no
+rule).
 
 Configurations: shapes from cfgs/anet_c3d_pdvc.yml (+ cfgs/anet_c3d_pdvcl.yml), cfgs/yc2_tsp_pdvc.yml as
 shipped and with the YouCook2 overrides of cfgs/yc2_tsn_pdvcl.yml:26,31, and the PDVC core of
@@ -81,13 +87,12 @@ class Trainer:
     """model + criterion + Adam(lr 5e-5, wd 1e-4) + grad clip 100 (cfgs/anet_c3d_pdvcl.yml:17,21; opts.py:104-105)."""
 
     def __init__(self, name_or_cfg, device, world_size=1, lr=5e-5, weight_decay=1e-4, grad_clip=100.0, amp=None,
-                 seed=0, dropout=None, mode="graphs", sync="flat"):
+                 seed=0, dropout=None, mode="graphs", sync="overlap"):
         """mode: 'graphs' = two CUDA graphs around the host matcher (pdvc/graphed.py; CUDA only), 'staged' = the same
         two stages eagerly, 'eager' = the reference's control flow (model.forward with the criterion inside).
-        sync (world_size > 1): 'flat' = gradients gathered into one buffer and all-reduced in ONE collective after
-        backward (the two-graph step hands all gradients over at the end of its two backward replays, so there is little
-        for DDP's bucket overlap to hide, while its per-parameter hooks cost one copy kernel per parameter); 'ddp' =
-        torch DistributedDataParallel."""
+        sync (world_size > 1): 'overlap' | 'flat' | 'ddp', see the module docstring."""
+        if sync not in ("overlap", "flat", "ddp"):
+            raise ValueError(f"sync must be 'overlap', 'flat' or 'ddp', got {sync!r}")
         spec = CONFIGS[name_or_cfg] if isinstance(name_or_cfg, str) else dict(cfg=name_or_cfg, n_gt=4, cap_len=12, amp=False)
         cfg = spec["cfg"]
         if dropout is not None:
@@ -121,7 +126,10 @@ class Trainer:
             from .graphed import StagedStep
             self.net = StagedStep(self.model, self.criterion, graphs=(mode == "graphs"), amp=self.amp)
         self.world_size, self.sync = world_size, sync
-        if world_size > 1 and sync == "flat":
+        self._buckets = None
+        if sync == "overlap" and mode != "eager":
+            self._setup_buckets()
+        if world_size > 1 and sync in ("flat", "overlap"):
             with torch.no_grad():                    # what DDP's constructor does: rank 0's weights and buffers everywhere
                 for t in list(self.model.parameters()) + list(self.model.buffers()):
                     torch.distributed.broadcast(t, 0)
@@ -146,7 +154,10 @@ class Trainer:
         """One training iteration on one video; returns the total loss as a device scalar of its own (not a view of a
         graph's static output) without synchronising, so a caller may read step i's loss after issuing step i+1."""
         dt = to_device(host_batch, self.device)
-        self.optimizer.zero_grad(set_to_none=True)
+        if self._sinks_live:
+            self._pending = []                       # .grad are views of the buckets, fully rewritten by the backward graphs
+        else:
+            self.optimizer.zero_grad(set_to_none=True)
         if self.mode == "eager":
             ctx = torch.autocast(self.device.type, dtype=torch.bfloat16) if self.amp else contextlib.nullcontext()
             with ctx:
@@ -159,12 +170,78 @@ class Trainer:
             else:
                 total, losses, _ = self.net(dt)       # graphs: autocast is baked into the captured stages
         total.backward()
-        if self.world_size > 1 and self.sync == "flat":
+        if self._sinks_live:
+            for work in self._pending:               # both buckets were issued during backward
+                work.wait()
+        elif self.world_size > 1 and self.sync == "overlap" and self._buckets is not None:
+            self._allreduce_buckets_after_backward()
+        elif self.world_size > 1 and self.sync in ("flat", "overlap"):
             self._allreduce_gradients()
         torch.nn.utils.clip_grad_norm_(self.params, self.grad_clip)
         self.optimizer.step()
         self.last_losses = losses
         return total.detach().clone()
+
+    # ---- sync='overlap' -----------------------------------------------------------------------------------------
+    def _setup_buckets(self):
+        """Two flat gradient buckets: [0] parameters only stage 2 reaches (the caption head: final when stage 2's
+        backward graph ends), [1] everything else (final when stage 1's ends).  With CUDA graphs the backward graphs copy
+        the gradients into the buckets themselves (graph_module grad_sinks) and `.grad` is a permanent view."""
+        first = {id(p) for p in self.net.stage2_parameters()}
+        groups = [[p for p in self.params if id(p) in first], [p for p in self.params if id(p) not in first]]
+        self._buckets = []
+        for group in groups:
+            flat = torch.zeros(sum(p.numel() for p in group), dtype=self.params[0].dtype, device=self.device)
+            views, offset = [], 0
+            for p in group:
+                views.append(flat[offset:offset + p.numel()].view_as(p))
+                offset += p.numel()
+            self._buckets.append((flat, group, views))
+        self._sinks_live = self.mode == "graphs"
+        if self._sinks_live:
+            self.net.grad_sinks = {id(p): v for _, group, views in self._buckets for p, v in zip(group, views)}
+            for _, group, views in self._buckets:
+                for p, v in zip(group, views):
+                    p.grad = v
+            if self.world_size > 1:
+                self._comm_stream = torch.cuda.Stream(self.device)
+                self.net.after_backward[2] = lambda: self._issue_bucket(0, side=True)
+                self.net.after_backward[1] = lambda: self._issue_bucket(1, side=False)
+
+    _sinks_live = False
+    _pending = ()
+
+    def _reduce_mean(self, flat, async_op=False):
+        dist = torch.distributed
+        if dist.get_backend() == "nccl":
+            return dist.all_reduce(flat, op=dist.ReduceOp.AVG, async_op=async_op)
+        work = dist.all_reduce(flat, async_op=False)
+        flat.div_(self.world_size)
+        return work
+
+    def _issue_bucket(self, index, side):
+        """Called from inside backward, right after a stage's backward graph was enqueued: start that bucket's all-reduce.
+        side=True: on the communication stream, so that the collective runs beside the next backward graph."""
+        flat = self._buckets[index][0]
+        current = torch.cuda.current_stream(self.device)
+        if side:
+            self._comm_stream.wait_stream(current)
+            with torch.cuda.stream(self._comm_stream):
+                work = self._reduce_mean(flat, async_op=True)
+            flat.record_stream(self._comm_stream)
+        else:
+            work = self._reduce_mean(flat, async_op=True)
+        self._pending.append(work)
+
+    def _allreduce_buckets_after_backward(self):
+        """'overlap' without CUDA graphs (mode='staged', the CPU/gloo tests): same two buckets, filled by concatenation
+        after backward -- the exchange pattern without the overlap."""
+        for flat, group, views in self._buckets:
+            grads = [p.grad if p.grad is not None else torch.zeros_like(p) for p in group]
+            torch.cat([g.reshape(-1) for g in grads], out=flat)
+            self._reduce_mean(flat)
+            for p, view in zip(group, views):
+                p.grad = view
 
     def _allreduce_gradients(self):
         """Mean of the gradients over the ranks: one concatenation, one all-reduce, .grad re-pointed into the flat buffer."""

@@ -8,7 +8,9 @@
  *     16-byte aligned at its base.
  *   - the CALLER owns and allocates every buffer (outputs need no pre-zeroing; the library
  *     zero-fills what it accumulates into).  The library allocates nothing, keeps no pointer
- *     after return and holds no mutable global state.
+ *     after return, reads no environment variable and holds no mutable global state beyond two
+ *     thread-local diagnostic integers (msda_last_launch_count / _path) and a cache of immutable
+ *     device properties (SM count, shared-memory opt-in done).
  *   - work is enqueued on `stream` (a cudaStream_t passed as void*; the reference uses
  *     at::cuda::getCurrentCUDAStream(), ms_deform_attn_cuda.cu:65,:135).  No entry point
  *     synchronises the host; all are CUDA-graph capturable.
@@ -233,8 +235,20 @@ int msda_lstm_cell_backward_f32(const float *grad_h, const float *grad_c, const 
                                 const float *c, const float *c_prev, float *grad_gates,
                                 float *grad_c_prev, int B, int H, void *stream);
 
-/* Number of kernels the last call on this thread launched (bench.py's gpu_launches). */
+/* Diagnostics (the library's only state: two thread-local integers, reset by every entry point).
+ * msda_last_launch_count: number of kernels / memsets the last call on this thread enqueued (bench.py's
+ * gpu_launches).  msda_last_launch_path: which kernel family served the last MSDeformAttn call -- the tests use it
+ * to prove that every family in csrc/ is reached. */
+enum {
+    MSDA_PATH_NONE = 0,
+    MSDA_PATH_LEAN = 1,    /* csrc/msda_lean.cuh: L*P <= 64, D*sizeof in {64,128,256,512} B */
+    MSDA_PATH_TILE = 2,    /* csrc/msda_tile.cuh: L*P <= 256 */
+    MSDA_PATH_FAST = 3,    /* csrc/msda_fast.cuh: any 16-byte divisible D */
+    MSDA_PATH_GENERIC = 4, /* csrc/msda_generic.cuh: any D, 2-D levels, f64, sampler */
+    MSDA_PATH_SMALL = 5    /* csrc/msda_small.cuh: single-phase kernels for launch-latency-bound problems */
+};
 int msda_last_launch_count(void);
+int msda_last_launch_path(void);
 
 #ifdef __cplusplus
 }

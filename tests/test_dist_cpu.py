@@ -87,9 +87,10 @@ def _ddp_worker(rank, world, port, out, sync):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("sync", ["flat", "ddp"])
+@pytest.mark.parametrize("sync", ["overlap", "flat", "ddp"])
 def test_two_rank_ddp_training_keeps_replicas_identical(sync):
-    """Both gradient-exchange modes of the Trainer: one flat all-reduce after backward, and torch DDP."""
+    """The gradient-exchange modes of the Trainer: two buckets (caption head / rest; on the GPU the first is reduced
+    while the stage-1 backward graph replays), one flat all-reduce after backward, and torch DDP."""
     world = 2
     mgr = mp.Manager()
     out = mgr.dict()
