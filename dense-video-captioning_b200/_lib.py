@@ -17,7 +17,7 @@ CSRC = os.path.join(_HERE, "csrc")
 F32, BF16, F64 = 0, 1, 2
 PAD_BORDER, PAD_ZEROS = 0, 1
 FLAG_ASSUME_1D, FLAG_FORCE_GENERIC = 1, 2
-PATH_NONE, PATH_LEAN, PATH_TILE, PATH_FAST, PATH_GENERIC, PATH_SMALL = range(6)
+PATH_NONE, PATH_LEAN, PATH_TILE, PATH_FAST, PATH_GENERIC, PATH_SMALL, PATH_PROJ = range(7)
 
 _vp, _i, _u, _sz, _ll = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint, ctypes.c_size_t, ctypes.c_longlong
 
@@ -42,6 +42,9 @@ SIGNATURES = {
     "msda_skinny_linear_f32": (_i, [_vp] * 4 + [_i] * 3 + [_vp]),
     "msda_lstm_cell_forward_f32": (_i, [_vp, _ll] + [_vp] * 5 + [_i, _i, _vp]),
     "msda_lstm_cell_backward_f32": (_i, [_vp] * 7 + [_i, _i, _vp]),
+    "msda_proj_forward": (_i, [_vp] * 8 + [_i] * 5 + [_vp]),
+    "msda_proj_dgrad": (_i, [_vp] * 6 + [_i] * 5 + [_vp]),
+    "msda_proj_wgrad": (_i, [_vp] * 8 + [_i] * 5 + [_vp]),
 }
 
 _lib = None

@@ -1,7 +1,7 @@
 from .ms_deform_attn_func import (CaptionAttendFunction, LSTMCellFunction, MSDeformAttnFunction, MSDeformAttnFusedFunction, MSDeformCapSampleFunction,
-                                  MSDeformSampleFunction, StepLinear,
+                                  MSDeformSampleFunction, ProjLinearFunction, StepLinear,
                                   get_default_padding_mode, ms_deform_attn_core_pytorch,
                                   set_default_padding_mode, skinny_linear)
 
 __all__ = ["MSDeformAttnFunction", "MSDeformAttnFusedFunction", "MSDeformSampleFunction", "MSDeformCapSampleFunction",
-           "ms_deform_attn_core_pytorch", "set_default_padding_mode", "get_default_padding_mode", "StepLinear", "skinny_linear", "LSTMCellFunction", "CaptionAttendFunction"]
+           "ms_deform_attn_core_pytorch", "set_default_padding_mode", "get_default_padding_mode", "StepLinear", "skinny_linear", "LSTMCellFunction", "CaptionAttendFunction", "ProjLinearFunction"]

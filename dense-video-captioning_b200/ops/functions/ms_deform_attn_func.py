@@ -412,6 +412,86 @@ class MSDeformCapSampleFunction(Function):
         return grad_value, None, None, grad_ref, grad_off, None
 
 
+class ProjLinearFunction(Function):
+    """The Linear projections of MSDeformAttn on the tcgen05 tensor cores (csrc/msda_proj.cuh).
+
+    apply(x, w0, b0, w1, b1, row_mask) -> y0                      (w1 is None: one layer)
+                                       -> (y0, y1)                (two layers that share x: sampling_offsets and
+                                                                   attention_weights, ms_deform_attn.py:99-100)
+    x (..., K); w_s (N_s, K); b_s (N_s) or None; row_mask (...) bool or None -- True rows of y0 are zero
+    (the masked_fill of ms_deform_attn.py:97-98).  Under torch.autocast(bf16) the operands are taken in bf16
+    (bf16 x bf16 -> fp32 accumulate); otherwise fp32 operands run as 3xTF32 split products (fp32-level accuracy).
+    Weight and bias gradients are produced in fp32."""
+
+    @staticmethod
+    def supported(x, w0, w1=None):
+        if not (x.is_cuda and x.dtype in (torch.float32, torch.bfloat16)):
+            return False
+        K, N0 = x.shape[-1], w0.shape[0]
+        N1 = w1.shape[0] if w1 is not None else 0
+        return K % 8 == 0 and N0 % 8 == 0 and N1 % 8 == 0 and (N1 == 0 or N0 % 128 == 0) and x.numel() > 0
+
+    @staticmethod
+    def forward(ctx, x, w0, b0, w1, b1, row_mask):
+        amp = torch.is_autocast_enabled("cuda")
+        dt = torch.get_autocast_dtype("cuda") if amp else x.dtype
+        _require(dt in (torch.float32, torch.bfloat16), "ProjLinearFunction takes float32 or bfloat16 operands")
+        K = x.shape[-1]
+        x2 = x.reshape(-1, K).to(dt).contiguous()
+        rows = x2.shape[0]
+        ws = [w.to(dt).contiguous() if w is not None else None for w in (w0, w1)]
+        bs = [b.float().contiguous() if b is not None else None for b in (b0, b1)]
+        N0, N1 = w0.shape[0], (w1.shape[0] if w1 is not None else 0)
+        mask = None
+        if row_mask is not None:
+            mask = row_mask.reshape(-1).contiguous().view(torch.uint8)
+            _require(mask.numel() == rows, "row_mask does not match the rows of x")
+        y0 = torch.empty((rows, N0), dtype=dt, device=x.device)
+        y1 = torch.empty((rows, N1), dtype=dt, device=x.device) if N1 else None
+        with torch.cuda.device(x.device):
+            rc = _lib.lib().msda_proj_forward(_ptr(x2), _ptr(ws[0]), _ptr(bs[0]), _ptr(ws[1]), _ptr(bs[1]), _ptr(mask),
+                                              _ptr(y0), _ptr(y1), rows, K, N0, N1, _DTYPES[dt], _stream(x.device))
+        _lib.check(rc, "msda_proj_forward")
+        ctx.save_for_backward(x2, ws[0], ws[1], mask)
+        ctx.meta = (x.shape, x.dtype, K, N0, N1, dt, b0 is not None, b1 is not None,
+                    w0.dtype, w1.dtype if w1 is not None else None)
+        lead = x.shape[:-1]
+        if N1:
+            return y0.view(*lead, N0), y1.view(*lead, N1)
+        return y0.view(*lead, N0)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, *grads):
+        x2, w0, w1, mask = ctx.saved_tensors
+        xshape, xdtype, K, N0, N1, dt, has_b0, has_b1, w0dt, w1dt = ctx.meta
+        rows = x2.shape[0]
+        dev = x2.device
+        dy0 = grads[0]
+        dy0 = (dy0 if dy0 is not None else torch.zeros((rows, N0), dtype=dt, device=dev)).reshape(rows, N0).to(dt).contiguous()
+        dy1 = None
+        if N1:
+            dy1 = grads[1]
+            dy1 = (dy1 if dy1 is not None else torch.zeros((rows, N1), dtype=dt, device=dev)).reshape(rows, N1).to(dt).contiguous()
+        lib = _lib.lib()
+        code = _DTYPES[dt]
+        dx = None
+        with torch.cuda.device(dev):
+            if ctx.needs_input_grad[0]:
+                dx = torch.empty((rows, K), dtype=dt, device=dev)
+                rc = lib.msda_proj_dgrad(_ptr(dy0), _ptr(dy1), _ptr(w0), _ptr(w1), _ptr(mask), _ptr(dx), rows, K, N0, N1, code, _stream(dev))
+                _lib.check(rc, "msda_proj_dgrad")
+                dx = dx.view(xshape).to(xdtype)
+            dw0 = torch.empty((N0, K), dtype=torch.float32, device=dev)
+            db0 = torch.empty((N0,), dtype=torch.float32, device=dev) if has_b0 else None
+            dw1 = torch.empty((N1, K), dtype=torch.float32, device=dev) if N1 else None
+            db1 = torch.empty((N1,), dtype=torch.float32, device=dev) if (N1 and has_b1) else None
+            rc = lib.msda_proj_wgrad(_ptr(dy0), _ptr(dy1), _ptr(x2), _ptr(mask), _ptr(dw0), _ptr(db0), _ptr(dw1), _ptr(db1),
+                                     rows, K, N0, N1, code, _stream(dev))
+            _lib.check(rc, "msda_proj_wgrad")
+        return (dx, dw0.to(w0dt), db0, dw1.to(w1dt) if dw1 is not None else None, db1, None)
+
+
 def ms_deform_attn_core_pytorch(value, value_spatial_shapes, sampling_locations, attention_weights,
                                 return_value=False):
     """Same call as the reference helper (func.py:41-68): no level_start_index argument, optional

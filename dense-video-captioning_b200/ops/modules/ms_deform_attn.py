@@ -14,7 +14,22 @@ from torch import nn
 from torch.nn.init import constant_, xavier_uniform_
 
 from ... import _lib
-from ..functions.ms_deform_attn_func import MSDeformAttnFunction, MSDeformAttnFusedFunction
+from ..functions.ms_deform_attn_func import MSDeformAttnFunction, MSDeformAttnFusedFunction, ProjLinearFunction
+
+# The module's Linear projections on the hand-written tcgen05 GEMMs (csrc/msda_proj.cuh; value_proj with its padding
+# mask in the epilogue, sampling_offsets and attention_weights as ONE GEMM, output_proj).  False: torch's library GEMMs.
+USE_PROJ_GEMM = True
+
+
+def _proj(x, lin0, lin1=None, row_mask=None):
+    """lin0(x) [, lin1(x)] with the row mask applied to lin0's output; tcgen05 path when the shapes allow it."""
+    w1 = lin1.weight if lin1 is not None else None
+    if USE_PROJ_GEMM and ProjLinearFunction.supported(x, lin0.weight, w1):
+        return ProjLinearFunction.apply(x, lin0.weight, lin0.bias, w1, lin1.bias if lin1 is not None else None, row_mask)
+    y0 = lin0(x)
+    if row_mask is not None:
+        y0 = y0.masked_fill(row_mask[..., None], float(0))
+    return (y0, lin1(x)) if lin1 is not None else y0
 
 
 def _is_power_of_2(n):
@@ -84,9 +99,7 @@ class _MSDeformFrontEnd(nn.Module):
         """value_proj + padding mask (ms_deform_attn.py:95-98) -> (N,S,M,D).  Callers that attend to the same memory
         many times (the caption LSTM, one call per word) may compute it once and pass it as `projected_value`."""
         N, Len_in, _ = input_flatten.shape
-        value = self.value_proj(input_flatten)
-        if input_padding_mask is not None:
-            value = value.masked_fill(input_padding_mask[..., None], float(0))
+        value = _proj(input_flatten, self.value_proj, row_mask=input_padding_mask)
         return value.view(N, Len_in, self.n_heads, self.d_model // self.n_heads)
 
     def _project(self, query, reference_points, input_flatten, input_spatial_shapes, input_padding_mask,
@@ -103,12 +116,16 @@ class _MSDeformFrontEnd(nn.Module):
             raise ValueError('Last dim of reference_points must be 1 or 2, but get {} instead.'.format(
                 reference_points.shape[-1]))
         value = projected_value if projected_value is not None else self.project_value(input_flatten, input_padding_mask)
-        if sampling_offsets is None:
-            sampling_offsets = self.sampling_offsets(query)
-        offsets = sampling_offsets.view(N, Len_q, self.n_heads, self.n_levels, self.n_points)
         logits = None
-        if need_logits:
-            logits = self.attention_weights(query).view(N, Len_q, self.n_heads, self.n_levels, self.n_points)
+        if sampling_offsets is None and need_logits:
+            sampling_offsets, logits = _proj(query, self.sampling_offsets, self.attention_weights)   # one GEMM
+        elif sampling_offsets is None:
+            sampling_offsets = _proj(query, self.sampling_offsets)
+        elif need_logits:
+            logits = _proj(query, self.attention_weights)
+        offsets = sampling_offsets.view(N, Len_q, self.n_heads, self.n_levels, self.n_points)
+        if logits is not None:
+            logits = logits.view(N, Len_q, self.n_heads, self.n_levels, self.n_points)
         return value, offsets, logits
 
     def _locations_and_weights(self, reference_points, offsets, logits, input_spatial_shapes):
@@ -166,5 +183,5 @@ class MSDeformAttn(_MSDeformFrontEnd):
                 loc, attn = loc.to(value.dtype), attn.to(value.dtype)
             output = MSDeformAttnFunction.apply(value, shapes2, input_level_start_index.contiguous(), loc, attn,
                                                 self.im2col_step, self.padding_mode, True)
-        output = self.output_proj(output)
+        output = _proj(output, self.output_proj)
         return output

@@ -235,6 +235,31 @@ int msda_lstm_cell_backward_f32(const float *grad_h, const float *grad_c, const 
                                 const float *c, const float *c_prev, float *grad_gates,
                                 float *grad_c_prev, int B, int H, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * The Linear projections of MSDeformAttn (pdvc/ops/modules/ms_deform_attn.py:95-100, :125) on the
+ * tcgen05 tensor cores, fp32 accumulation in tensor memory.  dtype MSDA_F32: 3xTF32 split products
+ * (fp32-level accuracy); MSDA_BF16: bf16 x bf16 -> fp32.
+ * One call covers ONE Linear layer or TWO that share their input (the sampling_offsets and
+ * attention_weights layers, :99-100: "segments" 0 and 1 with N0 / N1 output channels; N1 = 0 and
+ * NULL pointers for a single layer).
+ *   x (rows, K), w_s (N_s, K), b_s (N_s) fp32 or NULL, y_s / dy_s (rows, N_s), dx (rows, K);
+ *   dw_s (N_s, K) and db_s (N_s) are ALWAYS fp32 (gradients of the fp32 master parameters);
+ *   row_mask (rows) bytes or NULL, non-zero = padded frame: forward writes a zero row of y_0 (the
+ *   masked_fill of :97-98), the gradient entry points treat that row of dy_0 as zero (segment 1 is
+ *   never masked).
+ * Limits: K, N0, N1 multiples of 8; N0 a multiple of 128 when N1 > 0 (else MSDA_ERR_UNSUPPORTED and
+ * the caller uses its library GEMM).  All outputs fully overwritten; no workspace.
+ * ------------------------------------------------------------------------------------------- */
+int msda_proj_forward(const void *x, const void *w0, const float *b0, const void *w1, const float *b1,
+                      const unsigned char *row_mask, void *y0, void *y1, int rows, int K, int N0,
+                      int N1, int dtype, void *stream);
+int msda_proj_dgrad(const void *dy0, const void *dy1, const void *w0, const void *w1,
+                    const unsigned char *row_mask, void *dx, int rows, int K, int N0, int N1,
+                    int dtype, void *stream);
+int msda_proj_wgrad(const void *dy0, const void *dy1, const void *x, const unsigned char *row_mask,
+                    float *dw0, float *db0, float *dw1, float *db1, int rows, int K, int N0, int N1,
+                    int dtype, void *stream);
+
 /* Diagnostics (the library's only state: two thread-local integers, reset by every entry point).
  * msda_last_launch_count: number of kernels / memsets the last call on this thread enqueued (bench.py's
  * gpu_launches).  msda_last_launch_path: which kernel family served the last MSDeformAttn call -- the tests use it
@@ -245,7 +270,8 @@ enum {
     MSDA_PATH_TILE = 2,    /* csrc/msda_tile.cuh: L*P <= 256 */
     MSDA_PATH_FAST = 3,    /* csrc/msda_fast.cuh: any 16-byte divisible D */
     MSDA_PATH_GENERIC = 4, /* csrc/msda_generic.cuh: any D, 2-D levels, f64, sampler */
-    MSDA_PATH_SMALL = 5    /* csrc/msda_small.cuh: single-phase kernels for launch-latency-bound problems */
+    MSDA_PATH_SMALL = 5,   /* csrc/msda_small.cuh: single-phase kernels for launch-latency-bound problems */
+    MSDA_PATH_PROJ = 6     /* csrc/msda_proj.cuh: tcgen05 projection GEMMs */
 };
 int msda_last_launch_count(void);
 int msda_last_launch_path(void);
