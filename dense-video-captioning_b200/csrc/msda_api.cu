@@ -320,7 +320,6 @@ void fill_lean_args(TileArgs &a, const Dims &d, const LeanPlan &p, int pad_mode)
     a.win_rows = p.win_rows;
     a.gridK = p.gridK;
     a.hist_cap = p.hist_cap;
-    a.ring = d.N;     // backward: the accumulation image holds every video (lean_backward() may shorten it to a ring)
 }
 
 template <typename VT, int LPG, int NCH, int LPA, bool FUSED, bool BWD, int SPL = 1>
@@ -345,11 +344,11 @@ template <typename VT, bool FUSED, bool BWD> int launch_lean_shape(const TileArg
         return p.lpa == 16 ? launch_lean_inst<VT, LPG_, NCH_, 16, FUSED, BWD>(a, p, st)                  \
              : p.spl == 1  ? launch_lean_inst<VT, LPG_, NCH_, 32, FUSED, BWD>(a, p, st)                  \
                            : launch_lean_inst<VT, LPG_, NCH_, 32, FUSED, BWD, 2>(a, p, st);
-#ifndef MSDA_DEV_FAST   // development builds instantiate the headline shape only
+#ifndef MSDA_DEV_FAST   // development builds instantiate the headline shapes only (fp32 and bf16, D = 64)
     MSDA_LEAN_CASE(4, 1)
-    MSDA_LEAN_CASE(8, 1)
     MSDA_LEAN_CASE(8, 4)
 #endif
+    MSDA_LEAN_CASE(8, 1)
     MSDA_LEAN_CASE(8, 2)
 #undef MSDA_LEAN_CASE
     return MSDA_ERR_UNSUPPORTED;
@@ -391,9 +390,6 @@ size_t required_workspace(int N, int S, int M, int D, int dtype)
 {
     return dtype == MSDA_BF16 ? (size_t)N * S * M * D * sizeof(float) : 0;
 }
-// counters of the lean backward's just-in-time zeroing (optional part: without it the image is zero-filled up front)
-size_t jit_counter_bytes(int N) { return ((size_t)3 * N * sizeof(unsigned) + 255) / 256 * 256; }
-
 int memset_async(void *p, size_t bytes, cudaStream_t st)
 {
     ++g_launches;
@@ -413,54 +409,6 @@ int finish_bf16(const float *acc, void *grad_value, long long n, cudaStream_t st
         msda_cvt_f32_to_bf16_scalar_kernel<<<generic_grid(n), 256, 0, st>>>(acc, static_cast<__nv_bfloat16 *>(grad_value), n);
     }
     return check_launch();
-}
-
-// Lean backward with just-in-time zeroing (csrc/msda_lean.cuh): zero-fills only the first `ahead` videos of the
-// accumulation image, the kernel does the rest; bf16 keeps the fp32 image in a ring of `ring` videos and converts inside the
-// kernel, only the last `behind` videos are converted here.  Falls back to zero-filling everything (and, bf16, one
-// conversion pass) when the batch is too small or the caller gave no room for the counters.
-template <bool FUSED>
-int lean_backward(TileArgs &a, const Dims &d, const LeanPlan &lp, int dtype, int pad_mode, void *workspace, size_t ws_bytes,
-                  void *grad_value, cudaStream_t st)
-{
-    fill_lean_args(a, d, lp, pad_mode);
-    const size_t img = (size_t)d.S * d.M * d.D;                       // elements per video
-    const size_t base = required_workspace(d.N, d.S, d.M, d.D, dtype);
-    float *acc = dtype == MSDA_BF16 ? static_cast<float *>(workspace) : static_cast<float *>(grad_value);
-    a.gv_acc = acc;
-    a.ring = d.N;
-    // zero_ahead: about 1.25 waves of CTAs (3 resident per SM), at most ~48 MB of images (they must stay in L2)
-    static const int jit_env = env_int("MSDA_JIT", 1);
-    const long long cpv = (long long)lp.chunks * d.M;
-    long long ahead = (num_sms() * 15 / 4 + cpv - 1) / cpv;
-    const long long l2_cap = (48ll << 20) / (long long)(img * 4);
-    if (ahead > l2_cap) ahead = l2_cap;
-    if (ahead < 2) ahead = 2;
-    const bool jit = jit_env && workspace != nullptr && ws_bytes >= base + jit_counter_bytes(d.N) && d.N > 2 * ahead &&
-                     img % 8 == 0 && img * 4 < (1ull << 31);
-    if (!jit) {
-        if (int e = memset_async(acc, (size_t)d.N * img * 4, st)) return e;
-        if (int rc = launch_lean<FUSED, true>(a, lp, dtype, st)) return rc;
-        if (dtype == MSDA_BF16) return finish_bf16(acc, grad_value, (long long)d.N * img, st);
-        return MSDA_OK;
-    }
-    a.sync = reinterpret_cast<unsigned *>(static_cast<unsigned char *>(workspace) + base);
-    a.zero_ahead = (int)ahead;
-    if (dtype == MSDA_BF16) {
-        a.conv_behind = (int)ahead;
-        a.ring = (int)(2 * ahead + 2 < d.N ? 2 * ahead + 2 : d.N);
-        a.gv_out = grad_value;
-    }
-    if (int e = memset_async(a.sync, jit_counter_bytes(d.N), st)) return e;
-    if (int e = memset_async(acc, (size_t)ahead * img * 4, st)) return e;          // the first videos have no earlier CTAs
-    if (int rc = launch_lean<FUSED, true>(a, lp, dtype, st)) return rc;
-    if (dtype == MSDA_BF16) {
-        for (int n = d.N - a.conv_behind; n < d.N; ++n)                            // ... and the last ones no later CTAs
-            if (int rc = finish_bf16(acc + (size_t)(n % a.ring) * img, static_cast<__nv_bfloat16 *>(grad_value) + (size_t)n * img,
-                                     (long long)img, st))
-                return rc;
-    }
-    return MSDA_OK;
 }
 
 }  // namespace
@@ -498,8 +446,7 @@ const char *msda_error_string(int code)
 
 size_t msda_backward_workspace_bytes(int N, int S, int M, int D, int dtype)
 {
-    if (dtype == MSDA_F64 || N <= 0) return 0;
-    return required_workspace(N, S, M, D, dtype) + jit_counter_bytes(N);
+    return required_workspace(N, S, M, D, dtype);
 }
 
 int msda_ms_deform_attn_forward(const void *value, const int64_t *spatial_shapes, const int64_t *level_start_index,
@@ -580,23 +527,20 @@ int msda_ms_deform_attn_backward(const void *value, const int64_t *spatial_shape
     const bool try_chunked = one_d && !(flags & MSDA_FLAG_FORCE_GENERIC);
     const LeanPlan lp = try_chunked ? lean_plan(d, dtype, true) : LeanPlan{};
     const TilePlan tp = (try_chunked && !lp.ok) ? tile_plan(d, dtype, true) : TilePlan{};
-    if (lp.ok) {
-        TileArgs a{};
-        a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
-        a.loc = static_cast<const float *>(sampling_loc); a.attn = static_cast<const float *>(attn_weight);
-        a.grad_out = grad_output;
-        a.grad_loc = static_cast<float *>(grad_sampling_loc); a.grad_attn = static_cast<float *>(grad_attn_weight);
-        return lean_backward<false>(a, d, lp, dtype, pad_mode, workspace, workspace_bytes, grad_value, st);
-    }
     if (int e = memset_async(acc, (size_t)nv * (dtype == MSDA_F64 ? 8 : 4), st)) return e;
-    if (tp.ok) {
+    if (lp.ok || tp.ok) {
         TileArgs a{};
         a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
         a.loc = static_cast<const float *>(sampling_loc); a.attn = static_cast<const float *>(attn_weight);
         a.grad_out = grad_output; a.gv_acc = static_cast<float *>(acc);
         a.grad_loc = static_cast<float *>(grad_sampling_loc); a.grad_attn = static_cast<float *>(grad_attn_weight);
-        fill_tile_args(a, d, tp, pad_mode);
-        rc = launch_tile<false, true>(a, tp, dtype, st);
+        if (lp.ok) {
+            fill_lean_args(a, d, lp, pad_mode);
+            rc = launch_lean<false, true>(a, lp, dtype, st);
+        } else {
+            fill_tile_args(a, d, tp, pad_mode);
+            rc = launch_tile<false, true>(a, tp, dtype, st);
+        }
     } else if (one_d && lpg) {
         FastArgs a{};
         a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
@@ -704,13 +648,18 @@ int msda_fused_backward(const void *value, const int64_t *temporal_shapes, const
             TileArgs t{};
             t.value = value; t.shapes = temporal_shapes; t.lsi = level_start_index; t.shapes_stride = 1;
             t.ref = reference_points; t.offs = sampling_offsets; t.logits = attn_logits; t.R = R;
-            t.grad_out = grad_output;
-            t.grad_ref = grad_reference_points; t.grad_offs = grad_sampling_offsets; t.grad_logits = grad_attn_logits;
-            if (lp.ok) return lean_backward<true>(t, d, lp, dtype, pad_mode, workspace, workspace_bytes, grad_value, st);
             if (int e = memset_async(acc, (size_t)nv * 4, st)) return e;
-            t.gv_acc = static_cast<float *>(acc);
-            fill_tile_args(t, d, tp, pad_mode);
-            if (int trc = launch_tile<true, true>(t, tp, dtype, st)) return trc;
+            t.grad_out = grad_output; t.gv_acc = static_cast<float *>(acc);
+            t.grad_ref = grad_reference_points; t.grad_offs = grad_sampling_offsets; t.grad_logits = grad_attn_logits;
+            int trc;
+            if (lp.ok) {
+                fill_lean_args(t, d, lp, pad_mode);
+                trc = launch_lean<true, true>(t, lp, dtype, st);
+            } else {
+                fill_tile_args(t, d, tp, pad_mode);
+                trc = launch_tile<true, true>(t, tp, dtype, st);
+            }
+            if (trc) return trc;
             if (dtype == MSDA_BF16) return finish_bf16(static_cast<const float *>(acc), grad_value, nv, st);
             return MSDA_OK;
         }

@@ -37,8 +37,10 @@ __device__ unsigned long long g_phase_clk[2][16];
 #define MSDA_PHASE_FLUSH(K)
 #endif
 
+// CTAs per SM the backward is compiled for: 3 fit (shared memory) but cap the kernel at 80 registers, which spills 200
+// bytes per thread and is 5 % slower than 2 CTAs at 121 registers (0.910 vs 0.865 ms at the headline, tools/r2_ab.sh)
 #ifndef MSDA_BWD_MINB
-#define MSDA_BWD_MINB 3
+#define MSDA_BWD_MINB 2
 #endif
 #ifndef MSDA_FWD_MINB
 #define MSDA_FWD_MINB 4
@@ -143,32 +145,6 @@ __device__ __forceinline__ void window_update(int *win_lo, int *win_hi, int leve
         atomicMin(&win_lo[level], wlo);
         atomicMax(&win_hi[level], whi);
     }
-}
-
-// ---- just-in-time zeroing of the grad_value accumulation image (backward) ---------------------------------------------
-// The image used to be zero-filled by a cudaMemsetAsync before the kernel: 246 MB at the headline size that are written,
-// evicted from L2 and read back by the first reduction into every line (DRAM traffic 1.47x the algorithmic bytes).
-// Instead the CTAs of video n zero the image of video n + zero_ahead when they start -- CTAs are dispatched in grid order
-// (x, then y, then z = video), so that image is consumed about one wave later, while its lines are still in L2 -- and a
-// CTA takes its first reduction only after every zeroing CTA of its video has signalled.  All waits are on CTAs of
-// LOWER video index, i.e. on CTAs dispatched earlier (the in-order dispatch CUTLASS's serial split-K semaphores rely on).
-// bf16: the fp32 image is a ring of `ring` videos; the CTAs of video n convert video n - conv_behind to bf16 when they
-// finish (after its last reduction has been signalled) and a slot is re-zeroed only after its occupant was converted:
-// the whole fp32 image stays in L2 and the separate zero-fill and conversion passes disappear.
-__device__ __forceinline__ void spin_until(const unsigned *p, unsigned target)
-{
-    unsigned v;
-    for (;;) {
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-        if (v >= target) break;
-        __nanosleep(64);
-    }
-}
-// every thread of the CTA has finished its part (a __syncthreads precedes): publish it
-__device__ __forceinline__ void signal_done(unsigned *p)
-{
-    __threadfence();
-    atomicAdd(p, 1u);
 }
 
 // raw per-sample inputs (issued for all passes before anything is consumed)
@@ -546,27 +522,7 @@ __global__ void __launch_bounds__(kLeanThreads, (SPL == 1 ? MSDA_BWD_MINB : 2)) 
     int *start = reinterpret_cast<int *>(ent + ent_cap);
     unsigned char *Vw = reinterpret_cast<unsigned char *>(start + (a.hist_cap + 1 + 3) / 4 * 4);   // value window, win_rows x rb
 
-    // ---- just-in-time zeroing duty: this CTA's share of the accumulation slot of video n + zero_ahead ----
-    const bool jit = a.sync != nullptr;
-    const unsigned cpv = gridDim.x * gridDim.y;                       // CTAs per video
-    const int cid = blockIdx.y * gridDim.x + blockIdx.x;
-    const size_t img = (size_t)a.S * MD;                              // floats per video image
-    const int nz = n + a.zero_ahead;
-    const bool zero_duty = jit && nz < a.N;
-    if (zero_duty) {
-        if (nz >= a.ring) {                                           // ring (bf16): the slot's previous occupant has been converted
-            if (tid == 0) spin_until(a.sync + 2 * a.N + (nz - a.ring), cpv);
-            __syncthreads();
-        }
-        float4 *dst = reinterpret_cast<float4 *>(a.gv_acc + (size_t)(nz % a.ring) * img);
-        const int total4 = (int)(img >> 2);
-        const int share = (total4 + (int)cpv - 1) / (int)cpv;
-        const int z0 = cid * share, z1 = min(total4, z0 + share);
-        for (int i = z0 + tid; i < z1; i += kLeanThreads) dst[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-
-    lean_setup(a, blockIdx.x, tb);                                    // ends with a __syncthreads: the zero stores are issued
-    if (zero_duty && tid == 0) signal_done(a.sync + nz);
+    lean_setup(a, blockIdx.x, tb);
     MSDA_PHASE_MARK
 
     // ---- raw inputs of this lane's samples ----
@@ -731,7 +687,6 @@ __global__ void __launch_bounds__(kLeanThreads, (SPL == 1 ? MSDA_BWD_MINB : 2)) 
             }
         }
         cp_async_commit_wait_all();
-        if (jit && n >= a.zero_ahead && tid == 0) spin_until(a.sync + n, cpv);   // this video's image is zero
         __syncthreads();
         n_ent = n_ent_s;
     } else {
@@ -756,7 +711,6 @@ __global__ void __launch_bounds__(kLeanThreads, (SPL == 1 ? MSDA_BWD_MINB : 2)) 
             }
         }
         cp_async_commit_wait_all();
-        if (jit && n >= a.zero_ahead && tid == 0) spin_until(a.sync + n, cpv);   // this video's image is zero
         __syncthreads();
         MSDA_PHASE_MARK
         MSDA_PHASE_MARK
@@ -778,7 +732,7 @@ __global__ void __launch_bounds__(kLeanThreads, (SPL == 1 ? MSDA_BWD_MINB : 2)) 
         const int pp = (((pairs + NG - 1) / NG + 2) & ~3) + 1;
         const int gid = tid / LPG, j = lane % LPG;
         const VT *vslice = static_cast<const VT *>(a.value) + (size_t)n * a.S * MD + m * a.D + j * CH;
-        float *gslice = a.gv_acc + (size_t)(n % a.ring) * img + m * a.D + j * CH;
+        float *gslice = a.gv_acc + (size_t)n * a.S * MD + m * a.D + j * CH;
         const unsigned char *glane = Gs + j * 16;
         const unsigned char *vwlane = Vw + j * 16;
         constexpr int LPV = LPG >= 4 ? LPG / 4 : 1;   // lanes per reduced value
@@ -879,7 +833,6 @@ __global__ void __launch_bounds__(kLeanThreads, (SPL == 1 ? MSDA_BWD_MINB : 2)) 
         }
     }
     __syncthreads();
-    if (jit && a.conv_behind > 0 && tid == 0) signal_done(a.sync + a.N + n);      // this CTA's reductions into video n are out
     MSDA_PHASE_MARK
 
     // ---- per-sample gradients: the two dot products come back from the sample's entry ----
@@ -952,26 +905,6 @@ __global__ void __launch_bounds__(kLeanThreads, (SPL == 1 ? MSDA_BWD_MINB : 2)) 
                 }
             }
         }
-    }
-    // ---- bf16: conversion duty for video n - conv_behind (its CTAs were dispatched ~conv_behind videos earlier) ----
-    if (jit && a.conv_behind > 0 && n >= a.conv_behind) {
-        const int nc = n - a.conv_behind;
-        if (tid == 0) spin_until(a.sync + a.N + nc, cpv);
-        __syncthreads();
-        const float4 *src = reinterpret_cast<const float4 *>(a.gv_acc + (size_t)(nc % a.ring) * img);
-        uint4 *dst = reinterpret_cast<uint4 *>(static_cast<__nv_bfloat16 *>(a.gv_out) + (size_t)nc * img);
-        const int total8 = (int)(img >> 3);
-        const int share = (total8 + (int)cpv - 1) / (int)cpv;
-        const int c0 = cid * share, c1 = min(total8, c0 + share);
-        for (int i = c0 + tid; i < c1; i += kLeanThreads) {
-            const float4 x = __ldcg(src + 2 * i), y = __ldcg(src + 2 * i + 1);   // written by L2 reductions of other SMs
-            const __nv_bfloat162 p0 = __floats2bfloat162_rn(x.x, x.y), p1 = __floats2bfloat162_rn(x.z, x.w);
-            const __nv_bfloat162 p2 = __floats2bfloat162_rn(y.x, y.y), p3 = __floats2bfloat162_rn(y.z, y.w);
-            dst[i] = make_uint4(*reinterpret_cast<const unsigned *>(&p0), *reinterpret_cast<const unsigned *>(&p1),
-                                *reinterpret_cast<const unsigned *>(&p2), *reinterpret_cast<const unsigned *>(&p3));
-        }
-        __syncthreads();
-        if (tid == 0) signal_done(a.sync + 2 * a.N + nc);
     }
     MSDA_PHASE_MARK
     MSDA_PHASE_FLUSH(1)

@@ -57,12 +57,6 @@ struct TileArgs {
     int win_rows;  // forward: capacity of the shared-memory value window in rows (0: never stage)
     int gridK;     // lean kernels: 0 = a tile is Q consecutive queries; K > 0 = level-grid tiling into K time spans
     int hist_cap;  // lean backward: rows the sort histogram holds (a tile touching more is swept unsorted)
-    // lean backward, just-in-time zeroing of the accumulation image (NULL sync: the host zero-filled all of it):
-    unsigned *sync;    // [3][N] counters, zero at launch: zeroed[n], done[n], converted[n] (CTAs that finished that duty)
-    int ring;          // videos the accumulation image holds (video n lives in slot n % ring); N for fp32
-    int zero_ahead;    // CTAs of video n zero the slot of video n + zero_ahead before they start
-    int conv_behind;   // bf16: CTAs of video n convert video n - conv_behind to bf16 when they finish (0: fp32)
-    void *gv_out;      // bf16: grad_value (N,S,M,D) the conversion writes
 };
 
 // ---- small PTX wrappers -------------------------------------------------------------------
