@@ -16,7 +16,7 @@ CSRC = os.path.join(_HERE, "csrc")
 
 F32, BF16, F64 = 0, 1, 2
 PAD_BORDER, PAD_ZEROS = 0, 1
-FLAG_ASSUME_1D, FLAG_FORCE_GENERIC = 1, 2
+FLAG_ASSUME_1D, FLAG_FORCE_GENERIC, FLAG_NO_SMALL = 1, 2, 4
 PATH_NONE, PATH_LEAN, PATH_TILE, PATH_FAST, PATH_GENERIC, PATH_SMALL, PATH_PROJ = range(7)
 
 _vp, _i, _u, _sz, _ll = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint, ctypes.c_size_t, ctypes.c_longlong

@@ -12,6 +12,7 @@
 #include "msda_generic.cuh"
 #include "msda_tile.cuh"
 #include "msda_lean.cuh"
+#include "msda_small.cuh"
 #include "msda_capsample.cuh"
 #include "msda_steplinear.cuh"
 #include "msda_capattend.cuh"
@@ -360,6 +361,40 @@ template <bool FUSED, bool BWD> int launch_lean(const TileArgs &a, const LeanPla
                              : launch_lean_shape<__nv_bfloat16, FUSED, BWD>(a, p, st);
 }
 
+// ---- small problems: one CTA per (n, q), one warp per head (csrc/msda_small.cuh) -------------------------------------
+// lanes per value row, or 0 when the single-phase kernels do not take the problem
+int small_lanes(const Dims &d, int dtype, unsigned flags)
+{
+    if (flags & MSDA_FLAG_NO_SMALL) return 0;
+    static const int max_units = env_int("MSDA_SMALL_MAX", 1024);   // (n, q) pairs: above, the staged lean kernels win
+    if (dtype != MSDA_F32 && dtype != MSDA_BF16) return 0;
+    const int rb = d.D * (dtype == MSDA_BF16 ? 2 : 4);
+    if (rb != 64 && rb != 128 && rb != 256) return 0;
+    if (d.L * d.P > 32 || d.M > kSmallMaxHeads || (long long)d.N * d.Lq > max_units) return 0;
+    return rb / 16;
+}
+
+template <typename VT, bool FUSED, bool BWD> int launch_small(TileArgs &a, const Dims &d, int hl, int pad_mode, cudaStream_t st)
+{
+    a.N = d.N; a.S = d.S; a.M = d.M; a.D = d.D; a.L = d.L; a.Lq = d.Lq; a.P = d.P;
+    a.pad_mode = pad_mode;
+    a.LP = d.L * d.P;
+    a.invP = 1.f / (float)d.P;
+    const int grid = d.N * d.Lq, block = 32 * d.M;
+#define MSDA_SMALL_CASE(HL_)                                                                     \
+    case HL_:                                                                                    \
+        if (BWD) msda_bwd_small_kernel<VT, HL_, FUSED><<<grid, block, 0, st>>>(a);               \
+        else msda_fwd_small_kernel<VT, HL_, FUSED><<<grid, block, 0, st>>>(a);                   \
+        break;
+    switch (hl) {
+        MSDA_SMALL_CASE(4)
+        MSDA_SMALL_CASE(8)
+        default: MSDA_SMALL_CASE(16)
+    }
+#undef MSDA_SMALL_CASE
+    return check_launch(MSDA_PATH_SMALL);
+}
+
 int generic_grid(long long total)
 {
     long long blocks = (total + 255) / 256;
@@ -462,6 +497,14 @@ int msda_ms_deform_attn_forward(const void *value, const int64_t *spatial_shapes
     const bool one_d = (flags & MSDA_FLAG_ASSUME_1D) != 0;
     const int lpg = (flags & MSDA_FLAG_FORCE_GENERIC) ? 0 : fast_lpg(D, dtype);
     if (one_d && !(flags & MSDA_FLAG_FORCE_GENERIC)) {
+        if (const int hl = small_lanes(d, dtype, flags)) {
+            TileArgs a{};
+            a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
+            a.loc = static_cast<const float *>(sampling_loc); a.attn = static_cast<const float *>(attn_weight);
+            a.out = output;
+            return dtype == MSDA_F32 ? launch_small<float, false, false>(a, d, hl, pad_mode, st)
+                                     : launch_small<__nv_bfloat16, false, false>(a, d, hl, pad_mode, st);
+        }
         const LeanPlan lp = lean_plan(d, dtype, false);
         const TilePlan tp = lp.ok ? TilePlan{} : tile_plan(d, dtype, false);
         if (lp.ok || tp.ok) {
@@ -525,9 +568,21 @@ int msda_ms_deform_attn_backward(const void *value, const int64_t *spatial_shape
     const int lpg = (flags & MSDA_FLAG_FORCE_GENERIC) ? 0 : fast_lpg(D, dtype);
     int rc;
     const bool try_chunked = one_d && !(flags & MSDA_FLAG_FORCE_GENERIC);
+    if (int e = memset_async(acc, (size_t)nv * (dtype == MSDA_F64 ? 8 : 4), st)) return e;
+    if (const int hl = try_chunked ? small_lanes(d, dtype, flags) : 0) {
+        TileArgs a{};
+        a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
+        a.loc = static_cast<const float *>(sampling_loc); a.attn = static_cast<const float *>(attn_weight);
+        a.grad_out = grad_output; a.gv_acc = static_cast<float *>(acc);
+        a.grad_loc = static_cast<float *>(grad_sampling_loc); a.grad_attn = static_cast<float *>(grad_attn_weight);
+        rc = dtype == MSDA_F32 ? launch_small<float, false, true>(a, d, hl, pad_mode, st)
+                               : launch_small<__nv_bfloat16, false, true>(a, d, hl, pad_mode, st);
+        if (rc) return rc;
+        if (dtype == MSDA_BF16) return finish_bf16(static_cast<const float *>(acc), grad_value, nv, st);
+        return MSDA_OK;
+    }
     const LeanPlan lp = try_chunked ? lean_plan(d, dtype, true) : LeanPlan{};
     const TilePlan tp = (try_chunked && !lp.ok) ? tile_plan(d, dtype, true) : TilePlan{};
-    if (int e = memset_async(acc, (size_t)nv * (dtype == MSDA_F64 ? 8 : 4), st)) return e;
     if (lp.ok || tp.ok) {
         TileArgs a{};
         a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
@@ -576,7 +631,6 @@ int msda_fused_forward(const void *value, const int64_t *temporal_shapes, const 
                        void *output, int N, int S, int M, int D, int L, int Lq, int P, int R, int dtype, int pad_mode,
                        unsigned flags, void *stream)
 {
-    (void)flags;
     g_launches = 0; g_path = MSDA_PATH_NONE;
     const Dims d{N, S, M, D, L, Lq, P};
     if (int e = check_dims(d, dtype, pad_mode)) return e;
@@ -587,6 +641,14 @@ int msda_fused_forward(const void *value, const int64_t *temporal_shapes, const 
     const int lpg = fast_lpg(D, dtype);
     if (!lpg) return MSDA_ERR_UNSUPPORTED;   // callers fall back to the unfused entry points (still CUDA)
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (const int hl = small_lanes(d, dtype, flags)) {
+        TileArgs t{};
+        t.value = value; t.shapes = temporal_shapes; t.lsi = level_start_index; t.shapes_stride = 1;
+        t.ref = reference_points; t.offs = sampling_offsets; t.logits = attn_logits; t.R = R;
+        t.out = output;
+        return dtype == MSDA_F32 ? launch_small<float, true, false>(t, d, hl, pad_mode, st)
+                                 : launch_small<__nv_bfloat16, true, false>(t, d, hl, pad_mode, st);
+    }
     {
         const LeanPlan lp = lean_plan(d, dtype, false);
         const TilePlan tp = lp.ok ? TilePlan{} : tile_plan(d, dtype, false);
@@ -623,7 +685,6 @@ int msda_fused_backward(const void *value, const int64_t *temporal_shapes, const
                         int N, int S, int M, int D, int L, int Lq, int P, int R, int dtype, int pad_mode, unsigned flags,
                         void *stream)
 {
-    (void)flags;
     g_launches = 0; g_path = MSDA_PATH_NONE;
     const Dims d{N, S, M, D, L, Lq, P};
     if (int e = check_dims(d, dtype, pad_mode)) return e;

@@ -176,7 +176,9 @@ class MSDeformAttnFunction(Function):
         loc, attn = sampling_locations, attention_weights
         if value.dtype == torch.bfloat16:
             loc, attn = loc.float(), attn.float()
-        flags = (_lib.FLAG_ASSUME_1D if assume_1d else 0) | (_lib.FLAG_FORCE_GENERIC if force_generic else 0)
+        # force_generic: True -> the shape-generic kernels; "no_small" -> never the single-phase small-problem kernels (tests)
+        flags = (_lib.FLAG_ASSUME_1D if assume_1d else 0) | (_lib.FLAG_FORCE_GENERIC if force_generic is True else 0) | \
+                (_lib.FLAG_NO_SMALL if force_generic == "no_small" else 0)
         out = torch.empty((N, Lq, M * D), dtype=value.dtype, device=value.device)
         with torch.cuda.device(value.device):
             rc = _lib.lib().msda_ms_deform_attn_forward(
@@ -229,7 +231,7 @@ class MSDeformAttnFusedFunction(Function):
 
     @staticmethod
     def forward(ctx, value, temporal_shapes, level_start_index, reference_points, sampling_offsets,
-                attn_logits, padding_mode=None):
+                attn_logits, padding_mode=None, no_small=False):
         _check_cuda_contig(value=value, temporal_shapes=temporal_shapes, level_start_index=level_start_index,
                            reference_points=reference_points, sampling_offsets=sampling_offsets,
                            attn_logits=attn_logits)
@@ -256,9 +258,10 @@ class MSDeformAttnFusedFunction(Function):
             rc = _lib.lib().msda_fused_forward(
                 _ptr(value), _ptr(temporal_shapes), _ptr(level_start_index), _ptr(reference_points),
                 _ptr(sampling_offsets), _ptr(attn_logits), _ptr(out), N, S, M, D, L, Lq, P, R,
-                _DTYPES[value.dtype], pad, 0, _stream(value.device))
+                _DTYPES[value.dtype], pad, _lib.FLAG_NO_SMALL if no_small else 0, _stream(value.device))
         _lib.check(rc, "msda_fused_forward")
         ctx.pad = pad
+        ctx.flags = _lib.FLAG_NO_SMALL if no_small else 0
         ctx.save_for_backward(value, temporal_shapes, level_start_index, reference_points, sampling_offsets,
                               attn_logits)
         return out
@@ -284,9 +287,9 @@ class MSDeformAttnFusedFunction(Function):
             rc = lib.msda_fused_backward(
                 _ptr(value), _ptr(shapes), _ptr(lsi), _ptr(ref), _ptr(off), _ptr(logits), _ptr(grad_output),
                 _ptr(grad_value), _ptr(grad_ref), _ptr(grad_off), _ptr(grad_logits), _ptr(ws), ws_bytes,
-                N, S, M, D, L, Lq, P, R, code, ctx.pad, 0, _stream(value.device))
+                N, S, M, D, L, Lq, P, R, code, ctx.pad, ctx.flags, _stream(value.device))
         _lib.check(rc, "msda_fused_backward")
-        return grad_value, None, None, grad_ref, grad_off, grad_logits, None
+        return grad_value, None, None, grad_ref, grad_off, grad_logits, None, None
 
 
 class MSDeformSampleFunction(Function):

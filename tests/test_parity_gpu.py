@@ -77,12 +77,13 @@ def _oracle(t, shapes, pad):
 ONE_D = [c for c in cases.ALL_CORE_CASES if c not in ("ref_test_2d", "ragged_2d", "vec_2d")]
 
 
+@pytest.mark.parametrize("path", ["auto", "no_small"])     # auto: small problems take csrc/msda_small.cuh; no_small: the staged kernels
 @pytest.mark.parametrize("pad", ["border", "zeros"])
 @pytest.mark.parametrize("name", ONE_D)
-def test_core_fp32_vs_oracle(dvc, name, pad):
+def test_core_fp32_vs_oracle(dvc, name, pad, path):
     inp = cases.core_inputs(name)
     t = _round_inputs(inp, torch.float32)
-    got = _run_core(dvc, t, inp["shapes"], pad)
+    got = _run_core(dvc, t, inp["shapes"], pad, extra=(None, "no_small") if path == "no_small" else ())
     want = _oracle(t, inp["shapes"], pad)
     for g, w, what in zip(got, want, ("out", "grad_value", "grad_loc", "grad_attn")):
         _assert_close(_np64(g), w, torch.float32, f"{name}/{pad}/{what}")
@@ -114,14 +115,15 @@ def test_core_2d_and_fp64_vs_oracle(dvc, name, pad, dtype):
         _assert_close(_np64(g), w, dtype, f"{name}/{pad}/{what}")
 
 
+@pytest.mark.parametrize("path", ["auto", "no_small"])
 @pytest.mark.parametrize("pad", ["border", "zeros"])
 @pytest.mark.parametrize("name", ["yc2_dec", "anet_enc", "p8_d32", "p16_d128_l1", "edges", "uniform01"])
-def test_core_bf16_vs_oracle(dvc, name, pad):
+def test_core_bf16_vs_oracle(dvc, name, pad, path):
     inp = cases.core_inputs(name)
     if inp["value"].shape[-1] % 8:
         pytest.skip("bf16 vector path needs D % 8 == 0")
     t = _round_inputs(inp, torch.bfloat16)
-    got = _run_core(dvc, t, inp["shapes"], pad)
+    got = _run_core(dvc, t, inp["shapes"], pad, extra=(None, "no_small") if path == "no_small" else ())
     want = _oracle(t, inp["shapes"], pad)
     for g, w, what in zip(got, want, ("out", "grad_value", "grad_loc", "grad_attn")):
         _assert_close(_np64(g), w, torch.bfloat16, f"{name}/{pad}/bf16/{what}")
@@ -189,7 +191,8 @@ def _nudge_off_knots(inp, P):
     dict(seed=26, N=2, M=8, D=64, T=cases.level_lengths(120), Lq=70, P=16, R=2),   # L*P = 64, decoder tiling, boxes
     dict(seed=27, N=1, M=4, D=64, T=cases.level_lengths(90), Lq=33, P=10, R=1),    # L*P = 40
 ])
-def test_fused_vs_oracle(dvc, cfg, pad, dtype):
+@pytest.mark.parametrize("path", ["auto", "no_small"])
+def test_fused_vs_oracle(dvc, cfg, pad, dtype, path):
     if dtype == torch.bfloat16 and cfg["D"] < 32:
         pytest.skip("bf16 vector path needs D >= 32")
     inp = _nudge_off_knots(_fused_inputs(**cfg), cfg["P"])
@@ -201,7 +204,9 @@ def test_fused_vs_oracle(dvc, cfg, pad, dtype):
     gout = torch.from_numpy(inp["grad_out"]).to(dtype).to(dev)
     T = torch.from_numpy(inp["T"]).to(dev)
     lsi = torch.from_numpy(cases.level_start_index(cases.as_shapes2(inp["T"]))).to(dev)
-    out = dvc.MSDeformAttnFusedFunction.apply(value, T, lsi, ref, off, logits, pad)
+    out = dvc.MSDeformAttnFusedFunction.apply(value, T, lsi, ref, off, logits, pad, path == "no_small")
+    took = dvc._lib.lib().msda_last_launch_path()
+    assert (took != dvc._lib.PATH_SMALL) if path == "no_small" else True
     out.backward(gout)
     torch.cuda.synchronize()
     v64, r64, o64, l64, g64 = (_np64(x) for x in (value, ref, off, logits, gout))
@@ -362,7 +367,8 @@ def _encoder_inputs(seed, N, M, D, T0, P, jitter):
     dict(seed=35, N=1, M=4, D=64, T0=200, P=12, jitter=3.0),   # L*P = 48: SPL = 2 with dead lanes, P not a power of two
     dict(seed=36, N=3, M=2, D=128, T0=97, P=9, jitter=1.5),    # L*P = 36, D = 128, odd everything
 ])
-def test_encoder_geometry_vs_oracle(dvc, cfg, pad, dtype):
+@pytest.mark.parametrize("path", ["auto", "no_small"])
+def test_encoder_geometry_vs_oracle(dvc, cfg, pad, dtype, path):
     inp = _nudge_off_knots(_encoder_inputs(**cfg), cfg["P"])
     dev = "cuda"
     value = torch.from_numpy(inp["value"]).to(dtype).to(dev).requires_grad_(True)
@@ -372,7 +378,7 @@ def test_encoder_geometry_vs_oracle(dvc, cfg, pad, dtype):
     gout = torch.from_numpy(inp["grad_out"]).to(dtype).to(dev)
     T = torch.from_numpy(inp["T"]).to(dev)
     lsi = torch.from_numpy(cases.level_start_index(cases.as_shapes2(inp["T"]))).to(dev)
-    out = dvc.MSDeformAttnFusedFunction.apply(value, T, lsi, ref, off, logits, pad)
+    out = dvc.MSDeformAttnFusedFunction.apply(value, T, lsi, ref, off, logits, pad, path == "no_small")
     out.backward(gout)
     torch.cuda.synchronize()
     v64, r64, o64, l64, g64 = (_np64(x) for x in (value, ref, off, logits, gout))
@@ -451,8 +457,10 @@ def test_host_pipeline_equals_single_call(dvc):
     for _ in range(2):      # second run reuses the buffers
         got = pipe.run(*host)
         torch.cuda.synchronize()
-    assert torch.equal(got[0], out.detach().cpu())
-    assert torch.equal(got[2], o.grad.cpu()) and torch.equal(got[3], lg.grad.cpu())
+    # chunks of 4 videos are small problems (csrc/msda_small.cuh), the whole batch takes the staged kernels: same results up
+    # to fp32 rounding (different summation order of the 16 samples of a query)
+    for a, b in ((got[0], out.detach()), (got[2], o.grad), (got[3], lg.grad)):
+        assert float((a - b.cpu()).abs().max()) <= 1e-5 * float(b.abs().max())
     # grad_value is accumulated with float atomics: equal up to summation order
     assert float((got[1] - v.grad.cpu()).abs().max()) <= 1e-5 * float(v.grad.abs().max())
     with pytest.raises(RuntimeError):

@@ -143,6 +143,37 @@ def test_every_kernel_family_is_reached(dvc):
     assert seen["generic"] == L.PATH_GENERIC and seen["generic_2d"] == L.PATH_GENERIC
 
 
+def test_small_problem_kernels_are_taken_and_can_be_bypassed(dvc):
+    """configs[0] shapes go to the single-phase kernels (csrc/msda_small.cuh); MSDA_FLAG_NO_SMALL sends the same call to the
+    staged lean kernels; both agree with each other to fp32 rounding (the oracle parity of either is in test_parity_gpu.py)."""
+    L = dvc._lib
+    cfg = dict(seed=61, N=1, M=8, D=64, T=cases.level_lengths(200), Lq=100, P=4, R=2)
+    inp = _nudge_off_knots(_fused_inputs(**cfg), cfg["P"])
+    res = {}
+    for no_small in (False, True):
+        value = torch.from_numpy(inp["value"]).float().cuda().requires_grad_(True)
+        ref = torch.from_numpy(inp["ref"]).float().cuda().requires_grad_(True)
+        off = torch.from_numpy(inp["off"]).float().cuda().requires_grad_(True)
+        logits = torch.from_numpy(inp["logits"]).float().cuda().requires_grad_(True)
+        T = torch.from_numpy(inp["T"]).cuda()
+        lsi = torch.from_numpy(cases.level_start_index(cases.as_shapes2(inp["T"]))).cuda()
+        out = dvc.MSDeformAttnFusedFunction.apply(value, T, lsi, ref, off, logits, "border", no_small)
+        assert _path(dvc) == (L.PATH_LEAN if no_small else L.PATH_SMALL)
+        out.backward(torch.from_numpy(inp["grad_out"]).float().cuda())
+        res[no_small] = [out.detach(), value.grad, ref.grad, off.grad, logits.grad]
+    for a, b in zip(res[False], res[True]):
+        assert float((a - b).abs().max()) <= 1e-5 * float(b.abs().max()) + 1e-7
+    # the backward dispatch, through the C ABI on this thread (autograd runs backward on its own thread, whose thread-local
+    # diagnostics this thread cannot see): zero-fill of grad_value + ONE kernel
+    import bench
+    w = bench.make_workload(1, 200, 8, 64, 4, 4, "decoder", "cuda", seed=3)
+    op = bench.FusedOp(w)
+    op.forward()
+    assert _path(dvc) == L.PATH_SMALL and L.lib().msda_last_launch_count() == 1
+    op.backward()
+    assert _path(dvc) == L.PATH_SMALL and L.lib().msda_last_launch_count() == 2
+
+
 # ------------------------------------------------------------------------------------------------
 # sweep corners (BASELINE configs[4]: N up to 256, T0 up to 2000, P up to 16) with gradients vs the oracle
 # ------------------------------------------------------------------------------------------------
