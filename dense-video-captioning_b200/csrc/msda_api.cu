@@ -700,6 +700,20 @@ int msda_fused_backward(const void *value, const int64_t *temporal_shapes, const
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const long long nv = (long long)N * S * M * D;
     void *acc = dtype == MSDA_BF16 ? workspace : grad_value;
+    if (int e = memset_async(acc, (size_t)nv * 4, st)) return e;
+    if (const int hl = small_lanes(d, dtype, flags)) {
+        // the reference-point gradient is summed inside the CTA of its query: no zero-fill, no atomics
+        TileArgs t{};
+        t.value = value; t.shapes = temporal_shapes; t.lsi = level_start_index; t.shapes_stride = 1;
+        t.ref = reference_points; t.offs = sampling_offsets; t.logits = attn_logits; t.R = R;
+        t.grad_out = grad_output; t.gv_acc = static_cast<float *>(acc);
+        t.grad_ref = grad_reference_points; t.grad_offs = grad_sampling_offsets; t.grad_logits = grad_attn_logits;
+        const int src = dtype == MSDA_F32 ? launch_small<float, true, true>(t, d, hl, pad_mode, st)
+                                          : launch_small<__nv_bfloat16, true, true>(t, d, hl, pad_mode, st);
+        if (src) return src;
+        if (dtype == MSDA_BF16) return finish_bf16(static_cast<const float *>(acc), grad_value, nv, st);
+        return MSDA_OK;
+    }
     if (grad_reference_points)
         if (int e = memset_async(grad_reference_points, (size_t)N * Lq * L * R * 4, st)) return e;
     {
@@ -709,7 +723,6 @@ int msda_fused_backward(const void *value, const int64_t *temporal_shapes, const
             TileArgs t{};
             t.value = value; t.shapes = temporal_shapes; t.lsi = level_start_index; t.shapes_stride = 1;
             t.ref = reference_points; t.offs = sampling_offsets; t.logits = attn_logits; t.R = R;
-            if (int e = memset_async(acc, (size_t)nv * 4, st)) return e;
             t.grad_out = grad_output; t.gv_acc = static_cast<float *>(acc);
             t.grad_ref = grad_reference_points; t.grad_offs = grad_sampling_offsets; t.grad_logits = grad_attn_logits;
             int trc;
@@ -725,7 +738,6 @@ int msda_fused_backward(const void *value, const int64_t *temporal_shapes, const
             return MSDA_OK;
         }
     }
-    if (int e = memset_async(acc, (size_t)nv * 4, st)) return e;
     FastArgs a{};
     a.value = value; a.shapes = temporal_shapes; a.lsi = level_start_index; a.shapes_stride = 1;
     a.ref = reference_points; a.offs = sampling_offsets; a.logits = attn_logits; a.R = R;

@@ -15,6 +15,20 @@ import torch.nn.functional as F
 from torch import nn
 
 from ..ops.modules import MSDeformAttn
+from ..ops.modules.ms_deform_attn import _proj
+
+# The feed-forward Linears of the encoder / decoder layers (deformable_transformer.py:173-176, :247-250) on the same
+# tcgen05 GEMM kernels as MSDeformAttn's projections (csrc/msda_proj.cuh: bias in the epilogue, bias gradient in the
+# weight-gradient kernel) -- for fp32 operands, where that fusion beats cuBLAS' SIMT sgemm + separate bias kernels
+# (yc2 shape: 5.87 -> 5.83 ms/step); under bf16 autocast cuBLAS' tensor-core GEMMs are faster for these plain layers
+# (7.76 vs 7.82 ms/step, tools/pdvc_ab.py).  False: torch's library GEMMs always.
+USE_PROJ_FFN = True
+
+
+def _linear(x, lin):
+    if USE_PROJ_FFN and x.is_cuda and not torch.is_autocast_enabled("cuda"):
+        return _proj(x, lin)
+    return lin(x)
 
 
 def inverse_sigmoid(x, eps=1e-5):
@@ -43,7 +57,7 @@ class DeformableTransformerEncoderLayer(nn.Module):
         query = src if pos is None else src + pos
         attended = self.self_attn(query, reference_points, src, temporal_shapes, level_start_index, padding_mask)
         src = self.norm1(src + self.dropout1(attended))
-        hidden = self.linear2(self.dropout2(F.relu(self.linear1(src))))
+        hidden = _linear(self.dropout2(F.relu(_linear(src, self.linear1))), self.linear2)
         return self.norm2(src + self.dropout3(hidden))
 
 
@@ -99,7 +113,7 @@ class DeformableTransformerDecoderLayer(nn.Module):
         query = tgt if query_pos is None else tgt + query_pos
         sampled = self.cross_attn(query, reference_points, src, src_temporal_shapes, level_start_index, src_padding_mask)
         tgt = self.norm1(tgt + self.dropout1(sampled))
-        hidden = self.linear2(self.dropout3(F.relu(self.linear1(tgt))))
+        hidden = _linear(self.dropout3(F.relu(_linear(tgt, self.linear1))), self.linear2)
         return self.norm3(tgt + self.dropout4(hidden))
 
 
