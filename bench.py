@@ -47,13 +47,15 @@ def load_peaks():
 
 
 def load_traffic():
-    """DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of the headline kernels from the committed
-    `ncu --set full` capture (profiles/r1_traffic.json, written by tools/ncu_traffic.py); {} if absent."""
-    try:
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
-            return json.load(f)
-    except Exception:
-        return {}
+    """DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of the headline kernels from the latest committed
+    `ncu --set full` capture (profiles/r2_traffic.json, else r1_traffic.json; written by tools/ncu_traffic.py); {} if absent."""
+    for name in ("r2_traffic.json", "r1_traffic.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                return json.load(f)
+        except Exception:
+            continue
+    return {}
 
 
 def level_lengths(t0, n_levels=4):
@@ -599,6 +601,8 @@ def run_ours(args, world, rank, local):
     cfg = dict(HEADLINE)
     if args.batch:
         cfg["N"] = args.batch
+    if args.points:
+        cfg["P"] = args.points
     peak, peak_src = load_peaks()
     # weak scaling: every rank owns its own shard of cfg.N * world videos (seeded per rank)
     lo, hi = shard_batch(cfg["N"] * world, world, rank)
@@ -756,6 +760,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dtype", default="f32", choices=["f32", "bf16"])
     ap.add_argument("--batch", type=int, default=0, help="videos per GPU (default: headline config)")
+    ap.add_argument("--points", type=int, default=0, help="sampling points per level (default: headline config; experiments)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extra", action="store_true")
     ap.add_argument("--sweep", default="")

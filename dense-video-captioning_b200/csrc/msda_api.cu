@@ -363,10 +363,14 @@ template <bool FUSED, bool BWD> int launch_lean(const TileArgs &a, const LeanPla
 
 // ---- small problems: one CTA per (n, q), one warp per head (csrc/msda_small.cuh) -------------------------------------
 // lanes per value row, or 0 when the single-phase kernels do not take the problem
-int small_lanes(const Dims &d, int dtype, unsigned flags)
+int small_lanes(const Dims &d, int dtype, unsigned flags, bool backward = false)
 {
     if (flags & MSDA_FLAG_NO_SMALL) return 0;
-    static const int max_units = env_int("MSDA_SMALL_MAX", 1024);   // (n, q) pairs: above, the staged lean kernels win
+    // (n, q) pairs up to which the single-phase kernels win (graph-replayed, YC2 shapes: forward 3.6 / 4.5 us at 100 / 375
+    // queries against 5.5 / 5.3 us staged; backward 5.6 us at 100 queries against 11.7, but 11.4 against 10.3 at 375: one
+    // vector reduction per lane and tap is 25 MB of L2 atomics there, the staged kernel's per-row accumulation wins)
+    static const int max_fwd = env_int("MSDA_SMALL_MAX", 1024), max_bwd = env_int("MSDA_SMALL_MAX_BWD", 256);
+    const int max_units = backward ? max_bwd : max_fwd;
     if (dtype != MSDA_F32 && dtype != MSDA_BF16) return 0;
     const int rb = d.D * (dtype == MSDA_BF16 ? 2 : 4);
     if (rb != 64 && rb != 128 && rb != 256) return 0;
@@ -569,7 +573,7 @@ int msda_ms_deform_attn_backward(const void *value, const int64_t *spatial_shape
     int rc;
     const bool try_chunked = one_d && !(flags & MSDA_FLAG_FORCE_GENERIC);
     if (int e = memset_async(acc, (size_t)nv * (dtype == MSDA_F64 ? 8 : 4), st)) return e;
-    if (const int hl = try_chunked ? small_lanes(d, dtype, flags) : 0) {
+    if (const int hl = try_chunked ? small_lanes(d, dtype, flags, true) : 0) {
         TileArgs a{};
         a.value = value; a.shapes = spatial_shapes; a.lsi = level_start_index; a.shapes_stride = 2;
         a.loc = static_cast<const float *>(sampling_loc); a.attn = static_cast<const float *>(attn_weight);
@@ -701,7 +705,7 @@ int msda_fused_backward(const void *value, const int64_t *temporal_shapes, const
     const long long nv = (long long)N * S * M * D;
     void *acc = dtype == MSDA_BF16 ? workspace : grad_value;
     if (int e = memset_async(acc, (size_t)nv * 4, st)) return e;
-    if (const int hl = small_lanes(d, dtype, flags)) {
+    if (const int hl = small_lanes(d, dtype, flags, true)) {
         // the reference-point gradient is summed inside the CTA of its query: no zero-fill, no atomics
         TileArgs t{};
         t.value = value; t.shapes = temporal_shapes; t.lsi = level_start_index; t.shapes_stride = 1;

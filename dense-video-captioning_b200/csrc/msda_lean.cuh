@@ -45,6 +45,9 @@ __device__ unsigned long long g_phase_clk[2][16];
 #ifndef MSDA_FWD_MINB
 #define MSDA_FWD_MINB 4
 #endif
+#ifndef MSDA_FWD_MINB2      // two samples per lane (32 < L*P <= 64): fits 64 registers without spills; 4 instead of 2 CTAs/SM
+#define MSDA_FWD_MINB2 4    // took the P = 16 forward from 2.40 to 1.50 ms (N = 64, T0 = 1000; profiles/r2_notes.md)
+#endif
 constexpr int kLeanThreads = 256;
 constexpr int kLeanWarps = kLeanThreads / 32;
 constexpr int kLeanPasses = 4;   // units decoded per lane group and CTA (Q = kLeanPasses * units per pass)
@@ -301,7 +304,7 @@ __device__ __forceinline__ void stage_rows(unsigned char *dst, const unsigned ch
 // forward.  grid = (chunks, M, N); dynamic shared memory = [ records int4 x Q*LPT | value window ]
 // ---------------------------------------------------------------------------------------------
 template <typename VT, int LPG, int NCH, int LPA, bool FUSED, int SPL = 1>
-__global__ void __launch_bounds__(kLeanThreads, (SPL == 1 ? MSDA_FWD_MINB : 2)) msda_fwd_lean_kernel(const TileArgs a)
+__global__ void __launch_bounds__(kLeanThreads, (SPL == 1 ? MSDA_FWD_MINB : MSDA_FWD_MINB2)) msda_fwd_lean_kernel(const TileArgs a)
 {
     using IO = RowIO<VT, LPG, NCH>;
     constexpr int CH = Vec16<VT>::CH;

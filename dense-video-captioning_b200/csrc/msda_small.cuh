@@ -16,34 +16,25 @@
 
 namespace msda {
 
-constexpr int kSmallMaxHeads = 32;
+constexpr int kSmallMaxHeads = 16;   // warps per CTA (512 threads: 128 registers each, room for a batch of 8 row loads in flight)
+constexpr int kSmallBatch = 8;       // row loads issued back to back before the first one is consumed
 
-struct SmallLevels {
-    int T[kMaxLevels], start[kMaxLevels];
-};
-
-__device__ __forceinline__ void small_levels(const TileArgs &a, SmallLevels &lv)
-{
-    if ((int)threadIdx.x < a.L) {
-        lv.T[threadIdx.x] = (int)__ldg(a.shapes + (a.shapes_stride == 2 ? 2 * threadIdx.x + 1 : threadIdx.x));
-        lv.start[threadIdx.x] = (int)__ldg(a.lsi + threadIdx.x);
-    }
-    __syncthreads();
-}
-
-// decode of lane j's sample: attention weight (softmax over the warp when FUSED) and sampling geometry
+// decode of lane j's sample: attention weight (softmax over the warp when FUSED) and sampling geometry.  These kernels are
+// a chain of dependent memory round trips (cold: ~0.7 us each), so everything independent is issued together: the lane's
+// level length / start (read-only path, the same few words for every warp) and its raw sample inputs go out first.
 template <bool FUSED>
-__device__ __forceinline__ Decoded small_decode(const TileArgs &a, const SmallLevels &lv, int nq, int m, int lane, LaneLevel &c,
-                                                RawSample &raw)
+__device__ __forceinline__ Decoded small_decode(const TileArgs &a, int nq, int m, int lane, LaneLevel &c, RawSample &raw)
 {
     c.live = lane < a.LP;
     int l = lane / a.P;
     l = l < a.L ? l : a.L - 1;
     c.l = l;
-    c.T = lv.T[l];
-    c.start = lv.start[l];
-    c.tf = (float)c.T;
+    const long long Tl = __ldg(a.shapes + (a.shapes_stride == 2 ? 2 * l + 1 : l));
+    const long long st = __ldg(a.lsi + l);
     raw = load_raw<FUSED>(a, c, nq, (nq * a.M + m) * a.LP + lane, c.live);
+    c.T = (int)Tl;
+    c.start = (int)st;
+    c.tf = (float)c.T;
     float A = raw.y;
     if (FUSED) {
         const float mx = group_max<32>(c.live ? raw.y : -INFINITY);
@@ -61,13 +52,11 @@ __global__ void __launch_bounds__(32 * kSmallMaxHeads) msda_fwd_small_kernel(con
     constexpr int CH = Vec16<VT>::CH;
     constexpr int G = 32 / HL;      // lane groups per warp
     constexpr int SPI = G / 2;      // samples per step (two taps each)
-    __shared__ SmallLevels lv;
     const int m = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nq = blockIdx.x, n = nq / a.Lq;
-    small_levels(a, lv);
     LaneLevel c;
     RawSample raw;
-    const Decoded d = small_decode<FUSED>(a, lv, nq, m, lane, c, raw);
+    const Decoded d = small_decode<FUSED>(a, nq, m, lane, c, raw);
     const float k0 = c.live ? d.A * d.w0 : 0.f, k1 = c.live ? d.A * d.w1 : 0.f;
 
     const int grp = lane / HL, ch = lane % HL, tap = grp & 1, sub = grp >> 1;
@@ -77,19 +66,21 @@ __global__ void __launch_bounds__(32 * kSmallMaxHeads) msda_fwd_small_kernel(con
 #pragma unroll
     for (int k = 0; k < CH; ++k) acc[k] = 0.f;
     const int steps = (a.LP + SPI - 1) / SPI;
-#pragma unroll 4
-    for (int it = 0; it < steps; ++it) {
-        const int s = it * SPI + sub;                       // < 32 always (LP <= 32, SPI divides 32)
-        const int ra = __shfl_sync(kFull, d.r0, s & 31), rb = __shfl_sync(kFull, d.r1, s & 31);
-        const float ka = __shfl_sync(kFull, k0, s & 31), kb = __shfl_sync(kFull, k1, s & 31);
-        const int r = tap ? rb : ra;
-        const float kk = tap ? kb : ka;
-        if (s < a.LP && kk != 0.f) {
-            float v[CH];
-            Vec16<VT>::load(vslice + (size_t)r * MD, v);
+    for (int it0 = 0; it0 < steps; it0 += kSmallBatch) {
+        float v[kSmallBatch][CH], kk[kSmallBatch];
 #pragma unroll
-            for (int k = 0; k < CH; ++k) acc[k] = fmaf(kk, v[k], acc[k]);
+        for (int u = 0; u < kSmallBatch; ++u) {             // all row loads of the batch first (dead taps read row 0 of the slice)
+            const int s = (it0 + u) * SPI + sub;
+            const int ra = __shfl_sync(kFull, d.r0, s & 31), rb = __shfl_sync(kFull, d.r1, s & 31);
+            const float ka = __shfl_sync(kFull, k0, s & 31), kb = __shfl_sync(kFull, k1, s & 31);
+            kk[u] = s < a.LP ? (tap ? kb : ka) : 0.f;
+            const int r = kk[u] != 0.f ? (tap ? rb : ra) : 0;
+            Vec16<VT>::load(vslice + (size_t)r * MD, v[u]);
         }
+#pragma unroll
+        for (int u = 0; u < kSmallBatch; ++u)
+#pragma unroll
+            for (int k = 0; k < CH; ++k) acc[k] = fmaf(kk[u], v[u][k], acc[k]);
     }
     // lanes with equal channel chunk (one per group) hold partial sums
 #pragma unroll
@@ -106,16 +97,15 @@ __global__ void __launch_bounds__(32 * kSmallMaxHeads) msda_bwd_small_kernel(con
     constexpr int CH = Vec16<VT>::CH;
     constexpr int G = 32 / HL;
     constexpr int SPI = G / 2;
-    __shared__ SmallLevels lv;
     __shared__ float sdots[kSmallMaxHeads][64];            // [head][sample][tap]
     __shared__ float sref[2 * kMaxLevels];                 // [level][R]: sums over heads and points
     const int m = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nq = blockIdx.x, n = nq / a.Lq;
     for (int i = threadIdx.x; i < 2 * kMaxLevels; i += blockDim.x) sref[i] = 0.f;
-    small_levels(a, lv);
+    __syncthreads();
     LaneLevel c;
     RawSample raw;
-    const Decoded d = small_decode<FUSED>(a, lv, nq, m, lane, c, raw);
+    const Decoded d = small_decode<FUSED>(a, nq, m, lane, c, raw);
     const float k0 = c.live ? d.A * d.w0 : 0.f, k1 = c.live ? d.A * d.w1 : 0.f;
 
     const int grp = lane / HL, ch = lane % HL, tap = grp & 1, sub = grp >> 1;
@@ -125,28 +115,33 @@ __global__ void __launch_bounds__(32 * kSmallMaxHeads) msda_bwd_small_kernel(con
     float g[CH];
     Vec16<VT>::load(static_cast<const VT *>(a.grad_out) + (size_t)(nq * a.M + m) * a.D + ch * CH, g);
     const int steps = (a.LP + SPI - 1) / SPI;
-#pragma unroll 4
-    for (int it = 0; it < steps; ++it) {
-        const int s = it * SPI + sub;
-        const int ra = __shfl_sync(kFull, d.r0, s & 31), rb = __shfl_sync(kFull, d.r1, s & 31);
-        const float ka = __shfl_sync(kFull, k0, s & 31), kb = __shfl_sync(kFull, k1, s & 31);
-        const int r = tap ? rb : ra;
-        const float kk = tap ? kb : ka;
-        float p = 0.f;
-        if (s < a.LP) {
-            float v[CH];
-            Vec16<VT>::load(vslice + (size_t)r * MD, v);
+    for (int it0 = 0; it0 < steps; it0 += kSmallBatch) {
+        float v[kSmallBatch][CH], kk[kSmallBatch];
+        int rr[kSmallBatch];
 #pragma unroll
-            for (int k = 0; k < CH; ++k) p = fmaf(g[k], v[k], p);
-            if (kk != 0.f) {
-#pragma unroll
-                for (int k = 0; k < CH; k += 4)
-                    red_add_v4(gslice + (size_t)r * MD + k, kk * g[k], kk * g[k + 1], kk * g[k + 2], kk * g[k + 3]);
-            }
+        for (int u = 0; u < kSmallBatch; ++u) {             // all row loads of the batch first
+            const int s = (it0 + u) * SPI + sub;
+            const int ra = __shfl_sync(kFull, d.r0, s & 31), rb = __shfl_sync(kFull, d.r1, s & 31);
+            const float ka = __shfl_sync(kFull, k0, s & 31), kb = __shfl_sync(kFull, k1, s & 31);
+            kk[u] = s < a.LP ? (tap ? kb : ka) : 0.f;
+            rr[u] = s < a.LP ? (tap ? rb : ra) : 0;
+            Vec16<VT>::load(vslice + (size_t)rr[u] * MD, v[u]);
         }
 #pragma unroll
-        for (int off = HL / 2; off >= 1; off >>= 1) p += __shfl_xor_sync(kFull, p, off);
-        if (ch == 0 && s < a.LP) sdots[m][2 * s + tap] = p;
+        for (int u = 0; u < kSmallBatch; ++u) {
+            const int s = (it0 + u) * SPI + sub;
+            if (kk[u] != 0.f) {
+#pragma unroll
+                for (int k = 0; k < CH; k += 4)
+                    red_add_v4(gslice + (size_t)rr[u] * MD + k, kk[u] * g[k], kk[u] * g[k + 1], kk[u] * g[k + 2], kk[u] * g[k + 3]);
+            }
+            float p = 0.f;
+#pragma unroll
+            for (int k = 0; k < CH; ++k) p = fmaf(g[k], v[u][k], p);
+#pragma unroll
+            for (int off = HL / 2; off >= 1; off >>= 1) p += __shfl_xor_sync(kFull, p, off);
+            if (ch == 0 && s < a.LP) sdots[m][2 * s + tap] = p;
+        }
     }
     __syncwarp();
     // ---- per-sample gradients (lane j = sample j) ----
