@@ -369,6 +369,7 @@ __global__ void __launch_bounds__(kThreads, 1) msda_proj_kernel(const Args a)
     fence_after_sync();
     const uint32_t tmem_d = tmem_slot;
     int n_mma = 0;                                            // MMAs issued so far (every thread counts: block-uniform)
+    float bsum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // WGRAD: this thread's share of the bias gradient (8 channels)
 
     // ---- main loop over the reduction blocks of this CTA ----------------------------------------------------------
     // register ring: the global loads of kPrefetch reduction blocks are in flight at any time (these GEMMs are short and
@@ -404,25 +405,26 @@ __global__ void __launch_bounds__(kThreads, 1) msda_proj_kernel(const Args a)
         store_tile<T, TA>(sa, ra[u]);
         store_tile<T, TB>(sb, rb[u]);
         if (MODE == WGRAD && blockIdx.y == 0) {
-            // bias gradient: db[n] = sum over rows of dy[m][n] -- column sums of the A tile, taken from the registers
+            // bias gradient: db[n] = sum over rows of dy[m][n] -- column sums of the A tile.  The MN-chunk of a thread's tile
+            // chunks is fixed (chunk i -> MN-chunk i % NCM, and kThreads % NCM == 0), so the sums of its 8 channels stay in
+            // registers over the whole reduction loop; they meet in shared memory once, after the loop.
+            static_assert(kThreads % TA::NCM == 0, "a thread keeps one MN-chunk");
 #pragma unroll
             for (int j = 0; j < TA::PER_THREAD; ++j) {
-                int mn, kk, off;
-                TA::locate(tid + j * kThreads, mn, kk, off);
                 if (SPLIT) {
 #pragma unroll
                     for (int h = 0; h < Elem<T>::LOADS; ++h) {
-                        atomicAdd(&colsum[mn + 4 * h + 0], __uint_as_float(ra[u].v[j][h].x));
-                        atomicAdd(&colsum[mn + 4 * h + 1], __uint_as_float(ra[u].v[j][h].y));
-                        atomicAdd(&colsum[mn + 4 * h + 2], __uint_as_float(ra[u].v[j][h].z));
-                        atomicAdd(&colsum[mn + 4 * h + 3], __uint_as_float(ra[u].v[j][h].w));
+                        bsum[4 * h + 0] += __uint_as_float(ra[u].v[j][h].x);
+                        bsum[4 * h + 1] += __uint_as_float(ra[u].v[j][h].y);
+                        bsum[4 * h + 2] += __uint_as_float(ra[u].v[j][h].z);
+                        bsum[4 * h + 3] += __uint_as_float(ra[u].v[j][h].w);
                     }
                 } else {
                     const uint32_t wv[4] = {ra[u].v[j][0].x, ra[u].v[j][0].y, ra[u].v[j][0].z, ra[u].v[j][0].w};
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        atomicAdd(&colsum[mn + 2 * q], __uint_as_float(wv[q] << 16));
-                        atomicAdd(&colsum[mn + 2 * q + 1], __uint_as_float(wv[q] & 0xffff0000u));
+                        bsum[2 * q] += __uint_as_float(wv[q] << 16);
+                        bsum[2 * q + 1] += __uint_as_float(wv[q] & 0xffff0000u);
                     }
                 }
             }
@@ -462,6 +464,18 @@ __global__ void __launch_bounds__(kThreads, 1) msda_proj_kernel(const Args a)
         }
         n_mma += (BK / TA::MMA_K) * (SPLIT ? 6 : 1);
     }
+    }
+    if (MODE == WGRAD && blockIdx.y == 0) {
+        // threads tid, tid + NCM, ... hold the same 8 channels (MN-chunk tid % NCM): lanes l and l + 16 of a warp first
+        // (NCM = 16), then one shared-memory atomic per warp and channel
+        static_assert(TA::NCM == 16, "lane pairing below assumes 16 MN-chunks (BM = 128)");
+#pragma unroll
+        for (int k = 0; k < 8; ++k) bsum[k] += __shfl_xor_sync(0xffffffffu, bsum[k], 16);
+        if (lane < 16) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) atomicAdd(&colsum[lane * 8 + k], bsum[k]);
+        }
+        __syncthreads();
     }
     MSDA_PROJ_STAMP(2)
 
