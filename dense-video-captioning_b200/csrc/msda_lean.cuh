@@ -12,7 +12,8 @@
 //   * builds the tile's unit -> query table once per CTA in shared memory (64 threads) instead of per thread,
 //   * stages rows with one fixed 16-byte column per thread (pointer increments instead of div/mod per copy),
 //   * writes the two dot products of a sample back INTO its sorted entry (no separate dots array), keeps 4 instead
-//     of 9 registers per sample across the sweep and sizes the histogram by the window, so that three CTAs fit an SM,
+//     of 9 registers per sample across the sweep and sizes the histogram by the window (three CTAs would fit an SM's
+//     shared memory; the kernel is nevertheless compiled for two, see MSDA_BWD_MINB below),
 //   * carries acc1 -> acc0 and V[r+1] -> V[r] when the sweep moves to the next row (half the vector reductions),
 //   * sorts nothing when the tile's rows do not fit the histogram (scattered decoder queries on long videos):
 //     the same sweep then takes the samples one by one.

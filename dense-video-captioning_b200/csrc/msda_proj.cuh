@@ -32,6 +32,7 @@
 // The GEMMs here are small (100-375 rows, 256-512 columns, reduction 100-512): they are latency-bound, which is why
 // the reduction axis is split over a cluster -- more SMs stream the operands -- rather than tiles being made larger.
 #pragma once
+#include <cuda.h>          // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint)
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -307,6 +308,113 @@ __device__ __forceinline__ void store_tile(unsigned char *tile, const Regs<T, TI
     }
 }
 
+// ---- epilogue shared by the register-staged and the TMA-fed kernels ----------------------------------------------------
+// TMEM accumulators -> registers, split-K reduce-scatter over the cluster, bias / padding mask, coalesced stores, bias gradient.
+template <typename T, int MODE, int BK>
+__device__ __forceinline__ void proj_epilogue(const Args &a, unsigned char *smem, int ep_offset, uint64_t &done_bar, float *colsum,
+                                              uint32_t tmem_d, int n_mma, int nkb, uint32_t krank, int m0, int n0, int seg_n, int seg_m)
+{
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int Ntot = a.N0 + a.N1;
+    // ---- epilogue --------------------------------------------------------------------------------------------------
+    // warp w reads TMEM lanes 32*(w%4) .. +31 (the only ones it may access), columns (w/4)*BN/2 .. +BN/2 of every
+    // accumulator; the kAcc accumulators (independent MMA chains) are summed in registers
+    const int q = warp & 3, half = warp >> 2;
+    const int row_in_tile = 32 * q + lane;
+    constexpr int CPT = BN / 2;                               // columns per thread
+    float acc[CPT];
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) acc[c] = 0.f;
+    if (nkb > 0) {
+        mbar_wait(&done_bar, 0);
+        fence_after_sync();
+#pragma unroll
+        for (int j = 0; j < kAcc; ++j) {
+            if (j < n_mma) {                                  // accumulators that received at least one product
+#pragma unroll
+                for (int c = 0; c < CPT; c += 16) {
+                    float v[16];
+                    tmem_ld16(tmem_d + ((uint32_t)(32 * q) << 16) + (uint32_t)(j * BN + half * CPT + c), v);
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) acc[c + k] += v[k];
+                }
+            }
+        }
+    }
+    // split-K as a reduce-scatter over the cluster: CTA r finishes rows [r * RPC, (r + 1) * RPC) of the tile, RPC = BM / ksplit.
+    // Every CTA sends each accumulator row to the CTA that owns it (distributed shared memory; its own rows stay local):
+    // receive buffer [source rank][RPC rows][BN + 4] floats = BM * (BN + 4) floats whatever the split.
+    constexpr int EPS = BN + 4;                               // padded row: conflict-free float4 accesses
+    float *ep = reinterpret_cast<float *>(smem + ep_offset);
+    const int rpc = BM / a.ksplit;
+    {
+        const uint32_t owner = (uint32_t)(row_in_tile / rpc);
+        const int r_local = row_in_tile - (int)owner * rpc;
+        const uint32_t dst = (a.ksplit > 1 ? map_to_cta(ep, owner) : smem_u32(ep)) +
+                             (uint32_t)((((int)krank * rpc + r_local) * EPS + half * CPT) * 4);
+#pragma unroll
+        for (int c = 0; c < CPT; c += 4) {
+            if (a.ksplit > 1) st_cluster_v4(dst + c * 4, acc[c], acc[c + 1], acc[c + 2], acc[c + 3]);
+            else *reinterpret_cast<float4 *>(ep + row_in_tile * EPS + half * CPT + c) = make_float4(acc[c], acc[c + 1], acc[c + 2], acc[c + 3]);
+        }
+    }
+    float *redc = ep + BM * EPS;                              // bias-gradient partials [ksplit][BM], gathered in rank 0
+    if (MODE == WGRAD && blockIdx.y == 0 && tid < BM) {
+        if (a.ksplit > 1) {
+            const uint32_t dstc = map_to_cta(redc, 0) + (uint32_t)((krank * BM + tid) * 4);
+            asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(dstc), "f"(colsum[tid]) : "memory");
+        } else {
+            redc[tid] = colsum[tid];
+        }
+    }
+    if (a.ksplit > 1) cluster_sync_all();
+    else __syncthreads();
+    {
+        using OutT = typename OutType<T, MODE>::type;         // dx / y: the layer's data type; dw: always fp32
+        const int seg = MODE == FWD ? seg_n : seg_m;
+        const int base = seg ? a.N0 : 0;
+        const int row_lim = MODE == WGRAD ? (seg_m ? Ntot : a.N0) : a.rows;
+        const int col_lim = MODE == FWD ? (seg_n ? Ntot : a.N0) : a.K;
+        const long ld = MODE == FWD ? (seg_n ? a.N1 : a.N0) : a.K;
+        OutT *out = MODE == FWD ? static_cast<OutT *>(a.y[seg_n]) - base
+                  : MODE == DGRAD ? static_cast<OutT *>(a.dx)
+                                  : static_cast<OutT *>(a.dw[seg_m]) - (long)base * a.K;
+        const float *bias = MODE == FWD ? static_cast<const float *>(a.bias[seg_n]) : nullptr;
+        for (int idx = tid; idx < rpc * (BN / 4); idx += kThreads) {
+            const int r = idx / (BN / 4), c = (idx % (BN / 4)) * 4;
+            const int m = m0 + (int)krank * rpc + r, n = n0 + c;
+            if (m >= row_lim || n >= col_lim) continue;
+            float4 v = *reinterpret_cast<const float4 *>(ep + r * EPS + c);
+            for (int src = 1; src < a.ksplit; ++src) {
+                const float4 p = *reinterpret_cast<const float4 *>(ep + (src * rpc + r) * EPS + c);
+                v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+            }
+            if (MODE == FWD) {
+                if (bias != nullptr) {
+                    const float4 bv = __ldg(reinterpret_cast<const float4 *>(bias + (n - base)));
+                    v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+                }
+                if (a.mask != nullptr && seg_n == 0 && a.mask[m] != 0) v = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            OutT *dst = out + (long)m * ld + n;
+            if (sizeof(OutT) == 4) {
+                *reinterpret_cast<float4 *>(dst) = v;
+            } else {
+                const __nv_bfloat162 p0 = __floats2bfloat162_rn(v.x, v.y), p1 = __floats2bfloat162_rn(v.z, v.w);
+                *reinterpret_cast<uint2 *>(dst) = make_uint2(*reinterpret_cast<const uint32_t *>(&p0), *reinterpret_cast<const uint32_t *>(&p1));
+            }
+        }
+    }
+    if (MODE == WGRAD && blockIdx.y == 0 && krank == 0 && tid < BM) {
+        // bias gradient: rank 0 holds every k-slice's column sums
+        float sum = 0.f;
+        for (int src = 0; src < a.ksplit; ++src) sum += redc[src * BM + tid];
+        const int n = m0 + tid;
+        const int lim = seg_m ? Ntot : a.N0;
+        if (n < lim && a.db[seg_m] != nullptr) a.db[seg_m][n - (seg_m ? a.N0 : 0)] = sum;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------------
 // grid = (M tiles, N tiles, ksplit), cluster = (1, 1, ksplit); dynamic shared memory = Config::SMEM_BYTES
 // ---------------------------------------------------------------------------------------------------------------------
@@ -480,106 +588,125 @@ __global__ void __launch_bounds__(kThreads, 1) msda_proj_kernel(const Args a)
     MSDA_PROJ_STAMP(2)
 
     // ---- epilogue --------------------------------------------------------------------------------------------------
-    // warp w reads TMEM lanes 32*(w%4) .. +31 (the only ones it may access), columns (w/4)*BN/2 .. +BN/2 of every
-    // accumulator; the kAcc accumulators (independent MMA chains) are summed in registers
-    const int q = warp & 3, half = warp >> 2;
-    const int row_in_tile = 32 * q + lane;
-    constexpr int CPT = BN / 2;                               // columns per thread
-    float acc[CPT];
-#pragma unroll
-    for (int c = 0; c < CPT; ++c) acc[c] = 0.f;
-    if (nkb > 0) {
-        mbar_wait(&done_bar, 0);
-        fence_after_sync();
-#pragma unroll
-        for (int j = 0; j < kAcc; ++j) {
-            if (j < n_mma) {                                  // accumulators that received at least one product
-#pragma unroll
-                for (int c = 0; c < CPT; c += 16) {
-                    float v[16];
-                    tmem_ld16(tmem_d + ((uint32_t)(32 * q) << 16) + (uint32_t)(j * BN + half * CPT + c), v);
-#pragma unroll
-                    for (int k = 0; k < 16; ++k) acc[c + k] += v[k];
-                }
-            }
-        }
-    }
-    MSDA_PROJ_STAMP(3)
-    // split-K as a reduce-scatter over the cluster: CTA r finishes rows [r * RPC, (r + 1) * RPC) of the tile, RPC = BM / ksplit.
-    // Every CTA sends each accumulator row to the CTA that owns it (distributed shared memory; its own rows stay local):
-    // receive buffer [source rank][RPC rows][BN + 4] floats = BM * (BN + 4) floats whatever the split.
-    constexpr int EPS = BN + 4;                               // padded row: conflict-free float4 accesses
-    float *ep = reinterpret_cast<float *>(smem + CFG::EP_OFFSET);
-    const int rpc = BM / a.ksplit;
-    {
-        const uint32_t owner = (uint32_t)(row_in_tile / rpc);
-        const int r_local = row_in_tile - (int)owner * rpc;
-        const uint32_t dst = (a.ksplit > 1 ? map_to_cta(ep, owner) : smem_u32(ep)) +
-                             (uint32_t)((((int)krank * rpc + r_local) * EPS + half * CPT) * 4);
-#pragma unroll
-        for (int c = 0; c < CPT; c += 4) {
-            if (a.ksplit > 1) st_cluster_v4(dst + c * 4, acc[c], acc[c + 1], acc[c + 2], acc[c + 3]);
-            else *reinterpret_cast<float4 *>(ep + row_in_tile * EPS + half * CPT + c) = make_float4(acc[c], acc[c + 1], acc[c + 2], acc[c + 3]);
-        }
-    }
-    float *redc = ep + BM * EPS;                              // bias-gradient partials [ksplit][BM], gathered in rank 0
-    if (MODE == WGRAD && blockIdx.y == 0 && tid < BM) {
-        if (a.ksplit > 1) {
-            const uint32_t dstc = map_to_cta(redc, 0) + (uint32_t)((krank * BM + tid) * 4);
-            asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(dstc), "f"(colsum[tid]) : "memory");
-        } else {
-            redc[tid] = colsum[tid];
-        }
-    }
-    if (a.ksplit > 1) cluster_sync_all();
-    else __syncthreads();
-    MSDA_PROJ_STAMP(5)
-    {
-        using OutT = typename OutType<T, MODE>::type;         // dx / y: the layer's data type; dw: always fp32
-        const int seg = MODE == FWD ? seg_n : seg_m;
-        const int base = seg ? a.N0 : 0;
-        const int row_lim = MODE == WGRAD ? (seg_m ? Ntot : a.N0) : a.rows;
-        const int col_lim = MODE == FWD ? (seg_n ? Ntot : a.N0) : a.K;
-        const long ld = MODE == FWD ? (seg_n ? a.N1 : a.N0) : a.K;
-        OutT *out = MODE == FWD ? static_cast<OutT *>(a.y[seg_n]) - base
-                  : MODE == DGRAD ? static_cast<OutT *>(a.dx)
-                                  : static_cast<OutT *>(a.dw[seg_m]) - (long)base * a.K;
-        const float *bias = MODE == FWD ? static_cast<const float *>(a.bias[seg_n]) : nullptr;
-        for (int idx = tid; idx < rpc * (BN / 4); idx += kThreads) {
-            const int r = idx / (BN / 4), c = (idx % (BN / 4)) * 4;
-            const int m = m0 + (int)krank * rpc + r, n = n0 + c;
-            if (m >= row_lim || n >= col_lim) continue;
-            float4 v = *reinterpret_cast<const float4 *>(ep + r * EPS + c);
-            for (int src = 1; src < a.ksplit; ++src) {
-                const float4 p = *reinterpret_cast<const float4 *>(ep + (src * rpc + r) * EPS + c);
-                v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
-            }
-            if (MODE == FWD) {
-                if (bias != nullptr) {
-                    const float4 bv = __ldg(reinterpret_cast<const float4 *>(bias + (n - base)));
-                    v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
-                }
-                if (a.mask != nullptr && seg_n == 0 && a.mask[m] != 0) v = make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-            OutT *dst = out + (long)m * ld + n;
-            if (sizeof(OutT) == 4) {
-                *reinterpret_cast<float4 *>(dst) = v;
-            } else {
-                const __nv_bfloat162 p0 = __floats2bfloat162_rn(v.x, v.y), p1 = __floats2bfloat162_rn(v.z, v.w);
-                *reinterpret_cast<uint2 *>(dst) = make_uint2(*reinterpret_cast<const uint32_t *>(&p0), *reinterpret_cast<const uint32_t *>(&p1));
-            }
-        }
-    }
-    if (MODE == WGRAD && blockIdx.y == 0 && krank == 0 && tid < BM) {
-        // bias gradient: rank 0 holds every k-slice's column sums
-        float sum = 0.f;
-        for (int src = 0; src < a.ksplit; ++src) sum += redc[src * BM + tid];
-        const int n = m0 + tid;
-        const int lim = seg_m ? Ntot : a.N0;
-        if (n < lim && a.db[seg_m] != nullptr) a.db[seg_m][n - (seg_m ? a.N0 : 0)] = sum;
-    }
+    proj_epilogue<T, MODE, BK>(a, smem, CFG::EP_OFFSET, done_bar, colsum, tmem_d, n_mma, nkb, krank, m0, n0, seg_n, seg_m);
     MSDA_PROJ_STAMP(6)
     // ---- teardown ---------------------------------------------------------------------------------------------------
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_d, kAcc * BN);
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------------
+// bf16 operands fed by the Tensor Memory Accelerator (forward and data gradient; the weight gradient keeps the register
+// path because it also needs the operand values for the bias gradient, and so does a data gradient with a padding mask).
+// One elected thread issues cp.async.bulk.tensor boxes straight into the 128-byte-swizzled UMMA tiles (the TMA swizzle
+// IS the UMMA layout: a {64 x rows} box of a row-major matrix lands as rows of 128 bytes with chunk c of row r at c ^ r%8),
+// a second one issues the MMAs; full / empty mbarriers per stage, four stages; out-of-range rows and reduction tails are
+// zero-filled by the TMA.  Epilogue as above.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int kTmaStages = 4;
+struct TmaMaps {
+    CUtensorMap a[2];   // FWD: a[0] = x (rows, K).            DGRAD: a[s] = dy_s (rows, N_s)
+    CUtensorMap b[2];   // both: b[s] = w_s (N_s, K) -- K-major operand of the forward, MN-major operand of the data gradient
+};
+constexpr int kTmaStageBytes = (BM + BN) * kBK * 2;
+constexpr int kTmaEpOffset = kTmaStages * kTmaStageBytes;
+constexpr int kTmaSmemBytes = kTmaEpOffset + (BM * (BN + 4) + kMaxSplit * BM) * 4;
+
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kThreads, 1) msda_proj_tma_kernel(const Args a, const __grid_constant__ TmaMaps maps)
+{
+    using T = __nv_bfloat16;
+    constexpr int BK = kBK;
+    using CFG = Config<T, MODE, BK>;
+    using TA = typename CFG::TA;
+    using TB = typename CFG::TB;
+    static_assert(MODE == FWD || MODE == DGRAD, "TMA-fed kernel: forward and data gradient");
+    extern __shared__ __align__(1024) unsigned char smem[];
+    __shared__ __align__(8) uint64_t full_bar[kTmaStages];
+    __shared__ __align__(8) uint64_t empty_bar[kTmaStages];
+    __shared__ __align__(8) uint64_t done_bar;
+    __shared__ uint32_t tmem_slot;
+    __shared__ float colsum[BM];   // unused here (epilogue signature)
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+    const uint32_t krank = a.ksplit > 1 ? cluster_ctarank() : 0;
+    const int Ntot = a.N0 + a.N1;
+    const int Kred = MODE == FWD ? a.K : Ntot;
+    const int nkb_all = (Kred + BK - 1) / BK;
+    const int per = (nkb_all + a.ksplit - 1) / a.ksplit;
+    const int kb_lo = min((int)krank * per, nkb_all), kb_hi = min(kb_lo + per, nkb_all);
+    const int nkb = kb_hi - kb_lo;
+    const int seg_n = (MODE == FWD && n0 >= a.N0) ? 1 : 0;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < kTmaStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(&done_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&maps.a[0])) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&maps.b[0])) : "memory");
+    }
+    if (warp == 0) tmem_alloc(&tmem_slot, kAcc * BN);
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem_d = tmem_slot;
+    if (a.ksplit > 1) cluster_sync_all();   // every CTA of the cluster is running before any remote shared-memory store
+
+    if (warp == 0 && lane == 0) {
+        // ===== TMA producer =====
+        for (int i = 0; i < nkb; ++i) {
+            const int s = i % kTmaStages;
+            if (i >= kTmaStages) mbar_wait(&empty_bar[s], ((i / kTmaStages) - 1) & 1);
+            unsigned char *sa = smem + s * kTmaStageBytes, *sb = sa + TA::BYTES;
+            const int k0 = (kb_lo + i) * BK;
+            mbar_expect_tx(&full_bar[s], kTmaStageBytes);
+            if (MODE == FWD) {
+                tma_load_2d(sa, &maps.a[0], k0, m0, &full_bar[s]);
+                tma_load_2d(sb, &maps.b[seg_n], k0, n0 - (seg_n ? a.N0 : 0), &full_bar[s]);
+            } else {
+                const int sg = k0 >= a.N0 ? 1 : 0;          // reduction blocks never straddle the segments (N0 % 128 == 0)
+                const int kl = k0 - (sg ? a.N0 : 0);
+                tma_load_2d(sa, &maps.a[sg], kl, m0, &full_bar[s]);      // dy_s: box {64 channels n, 128 rows}
+                tma_load_2d(sb, &maps.b[sg], n0, kl, &full_bar[s]);      // w_s : box {64 columns k, 64 rows n} = MN-major tile
+            }
+        }
+    } else if (warp == 1 && lane == 0) {
+        // ===== MMA issuer =====
+        int j = 0;
+        for (int i = 0; i < nkb; ++i) {
+            const int s = i % kTmaStages;
+            mbar_wait(&full_bar[s], (i / kTmaStages) & 1);
+            fence_after_sync();
+            const uint32_t a_addr = smem_u32(smem + s * kTmaStageBytes), b_addr = a_addr + TA::BYTES;
+#pragma unroll
+            for (int ks = 0; ks < BK / TA::MMA_K; ++ks) {
+                umma(tmem_d + (uint32_t)((j % kAcc) * BN), TA::descriptor(a_addr + ks * TA::KSTEP_BYTES),
+                     TB::descriptor(b_addr + ks * TB::KSTEP_BYTES), CFG::IDESC, j >= kAcc ? 1u : 0u);
+                ++j;
+            }
+            umma_commit(&empty_bar[s]);
+            if (i == nkb - 1) umma_commit(&done_bar);
+        }
+    }
+    __syncwarp();
+    const int n_mma = nkb * (BK / TA::MMA_K);
+    proj_epilogue<T, MODE, BK>(a, smem, kTmaEpOffset, done_bar, colsum, tmem_d, n_mma, nkb, krank, m0, n0, seg_n, 0);
     fence_before_sync();
     __syncthreads();
     if (warp == 0) tmem_dealloc(tmem_d, kAcc * BN);
