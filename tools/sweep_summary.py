@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""profiles/r1_sweep.json (bench.py --sweep) -> profiles/r1_sweep_summary.md"""
+"""profiles/rN_sweep.json (bench.py --sweep) -> profiles/rN_sweep_summary.md   usage: tools/sweep_summary.py [sweep.json]"""
 import json
 import os
 import sys
@@ -13,15 +13,22 @@ out = [f"# BASELINE configs[4] sweep (bench.py --sweep), B200, fused boundary, H
        "Encoder rows (Lq = S) read every value row, so `frac` is a true HBM fraction.  **Decoder rows (Lq = 100) sample only",
        "100 x 8 x L x P x 2 of the S x 8 value rows per video**: the forward never touches most of `value`, so its algorithmic-byte",
        "figure over-counts real traffic and can exceed the peak (e.g. 7.6 TB/s 'achieved' at N=256, T0=2000); the backward still",
-       "writes all of `grad_value`.  Decoder `frac` is listed for completeness, not as a bandwidth claim.", ""]
+       "writes all of `grad_value`.  Decoder `frac` is listed for completeness, not as a bandwidth claim.", "",
+       "`on-chip` (encoder rows) = the forward's time floor from its interpolation taps alone -- N*Lq*M*L*P samples x 2 rows x D*e bytes of",
+       "shared memory at one 128-byte wavefront per clock and SM (148 SMs, 1965 MHz) -- divided by the measured forward time: how close the",
+       "forward is to the bound of a per-sample shared-memory gather (DESIGN.md section 4).", ""]
 for kind in ("encoder", "decoder"):
     for dtype in ("f32", "bf16"):
-        out += [f"## {kind}, {dtype}", "", "| N | T0 | S | P | fwd us | bwd us | Mqueries/s | fwd GB/s | bwd GB/s | frac |", "|---|---|---|---|---|---|---|---|---|---|"]
+        out += [f"## {kind}, {dtype}", "", "| N | T0 | S | P | fwd us | bwd us | Mqueries/s | fwd GB/s | bwd GB/s | frac | on-chip |", "|---|---|---|---|---|---|---|---|---|---|---|"]
         for r in sorted((r for r in rows if r["kind"] == kind and r["dtype"] == dtype), key=lambda r: (r["P"], r["T0"], r["N"])):
+            e = 2 if dtype == "bf16" else 4
+            floor_us = r["N"] * r["Lq"] * 8 * 4 * r["P"] * 2 * 64 * e / 128 / 148 / 1965.0
+            onchip = f"{floor_us / r['fwd_us']:.2f}" if kind == "encoder" else "-"
             out.append(f"| {r['N']} | {r['T0']} | {r['S']} | {r['P']} | {r['fwd_us']:.1f} | {r['bwd_us']:.1f} | {r['queries_per_s'] / 1e6:.2f} | "
-                       f"{r['fwd_gbs']:.0f} | {r['bwd_gbs']:.0f} | {r['fwd_bwd_frac_hbm']:.3f} |")
+                       f"{r['fwd_gbs']:.0f} | {r['bwd_gbs']:.0f} | {r['fwd_bwd_frac_hbm']:.3f} | {onchip} |")
         out.append("")
-open(os.path.join(ROOT, "profiles", "r1_sweep_summary.md"), "w").write("\n".join(out))
+dst = src.replace(".json", "_summary.md")
+open(dst, "w").write("\n".join(out))
 enc = [r for r in rows if r["kind"] == "encoder"]
 best = max(enc, key=lambda r: r["fwd_bwd_frac_hbm"])
 print(len(rows), "rows; best encoder point:", best)
