@@ -13,6 +13,13 @@ them with tests/cases.fill_parameters().  Dropout is 0 so that the training-mode
                        (100 queries, T = 200, vocab 1607, max_eseq_length 20)                 BASELINE configs[1](b)
         newmodel_core  cfgs/yc2_newModel_sound.yml:8-19 (768-d features, 3+3 layers, 100 queries, T = 200): the PDVC
                        core of the MViT+HuBERT model                                          BASELINE configs[3]
+        anet_c3d_refcuda   anet_c3d with the padding semantics of the reference's GPU build: MSDeformAttn (encoder,
+                       decoder) samples with ZERO padding, as MSDeformAttnFunction's CUDA kernel does
+                       (ms_deform_im2col_cuda.cuh:286-289; module call site ms_deform_attn.py:120-122), while the caption
+                       head's MSDeformAttnCap stays on grid_sample / border (ms_deform_attn_for_caption.py:120-121 calls
+                       the PyTorch core unconditionally).  The reference's extension is not built here, so the module's
+                       core call is redirected to the oracle's grid_sample restatement with padding_mode="zeros" -- the
+                       only patched line; everything else is the unmodified reference.
 """
 import collections
 import os
@@ -29,7 +36,7 @@ import cases  # noqa: E402
 REF = "/root/reference"
 
 
-def load_reference(cfg_path, overrides):
+def load_reference(cfg_path, overrides, zero_padded_attn=False):
     for name in ("MultiScaleDeformableAttention", "colorlog", "matplotlib", "matplotlib.pyplot"):
         sys.modules.setdefault(name, types.ModuleType(name))
     sys.modules["matplotlib"].use = lambda *a, **k: None
@@ -41,6 +48,14 @@ def load_reference(cfg_path, overrides):
     for k, v in overrides.items():
         setattr(opt, k, v)
     from pdvc.pdvc import build
+    if zero_padded_attn:
+        sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+        from oracle import core_pytorch
+        import pdvc.ops.modules.ms_deform_attn as ref_mod
+
+        def zero_padded_core(value, shapes, loc, attn, return_value=False):
+            return core_pytorch.core(value, shapes, loc, attn, return_value=return_value, padding_mode="zeros")
+        ref_mod.ms_deform_attn_core_pytorch = zero_padded_core      # MSDeformAttn only; the caption module keeps its own import
     model, criterion, _ = build(opt)
     return opt, model, criterion
 
@@ -50,6 +65,7 @@ FIXTURES = {
     "yc2shape": ("cfgs/yc2_tsp_pdvc.yml", dict(num_queries=100, frame_embedding_num=200, vocab_size=1607, max_eseq_length=20),
                  dict(seed=6, n_gt=6, cap_len=10)),
     "newmodel_core": ("cfgs/yc2_newModel_sound.yml", dict(), dict(seed=7, n_gt=5, cap_len=8)),
+    "anet_c3d_refcuda": ("cfgs/anet_c3d_pdvc.yml", dict(vocab_size=300), dict(seed=5, n_gt=4, cap_len=9)),
 }
 
 
@@ -58,7 +74,8 @@ def main():
     cfg_path, overrides, batch = FIXTURES[fixture]
     torch.manual_seed(0)
     torch.set_default_dtype(torch.float64)   # the reference creates helper tensors with the default dtype
-    opt, model, criterion = load_reference(cfg_path, dict(transformer_dropout_prob=0.0, drop_prob=0.0, **overrides))
+    opt, model, criterion = load_reference(cfg_path, dict(transformer_dropout_prob=0.0, drop_prob=0.0, **overrides),
+                                           zero_padded_attn=fixture.endswith("_refcuda"))
     model.double().train()
     criterion.double()
     cases.fill_parameters(model)

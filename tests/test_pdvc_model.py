@@ -178,6 +178,40 @@ def test_cuda_model_matches_reference_model_fp32(fixture):
 
 
 @pytest.mark.gpu
+def test_cuda_model_zeros_mode_matches_reference_gpu_build_semantics():
+    """set_default_padding_mode('zeros') = the reference's GPU build: MSDeformAttn (encoder, decoder) zero-padded like
+    MSDeformAttnFunction's CUDA kernel (ms_deform_im2col_cuda.cuh:286-289), MSDeformAttnCap still border -- the caption
+    module calls the grid_sample core on every device (ms_deform_attn_for_caption.py:120-121).  Golden:
+    pdvc_anet_c3d_refcuda.npz (make_golden_pdvc.py).  The two goldens differ by 1e-5 ... 2e-4 per loss term, so on top of
+    the usual bars the run must sit at least 10x closer to the zero-padded numbers wherever the two goldens are apart."""
+    from dense_video_captioning_b200.ops import functions as F
+    from dense_video_captioning_b200.ops.modules import MSDeformAttnCap
+    from dense_video_captioning_b200.pdvc import build
+    golden, border = load_golden("pdvc_anet_c3d_refcuda"), load_golden("pdvc_anet_c3d")
+    cfg = _cfg(golden)
+    prev = F.get_default_padding_mode()
+    F.set_default_padding_mode("zeros")
+    try:
+        model, criterion = build(cfg)
+        model.cuda().train()
+        criterion.cuda()
+        cases.fill_parameters(model)
+        caps = [m for m in model.modules() if isinstance(m, MSDeformAttnCap)]
+        assert caps and all(m.padding_mode == "border" for m in caps)
+        out, loss, total = _run(model, criterion, _batch(cfg, torch.float32, "cuda", golden))
+        torch.cuda.synchronize()
+    finally:
+        F.set_default_padding_mode(prev)
+    _check(golden, model, out, loss, total, rel_loss=2e-4, rel_grad=2e-3)
+    z = dict(zip([str(n) for n in golden["loss_names"]], golden["loss_values"]))
+    b = dict(zip([str(n) for n in border["loss_names"]], border["loss_values"]))
+    apart = [k for k in z if abs(z[k] - b[k]) > 2e-5]
+    assert len(apart) >= 3, apart
+    for k in apart:
+        assert 10 * abs(float(loss[k]) - z[k]) < abs(float(loss[k]) - b[k]), (k, float(loss[k]), z[k], b[k])
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("fixture", ["yc2shape", "newmodel_core"])
 def test_cuda_model_bf16_autocast_tracks_reference_model(fixture):
     """bf16 autocast (BASELINE configs[3]: bf16 GEMMs, MSDA kernels on bf16 values with the index side in fp32) against
