@@ -17,6 +17,8 @@ CSRC = os.path.join(_HERE, "csrc")
 F32, BF16, F64 = 0, 1, 2
 PAD_BORDER, PAD_ZEROS = 0, 1
 FLAG_ASSUME_1D, FLAG_FORCE_GENERIC, FLAG_NO_SMALL = 1, 2, 4
+STATIC_SCRATCH_BYTES = 16 << 20    # MSDA_STATIC_SCRATCH_BYTES
+ERR_STATIC_SCRATCH = -8
 PATH_NONE, PATH_LEAN, PATH_TILE, PATH_FAST, PATH_GENERIC, PATH_SMALL, PATH_PROJ = range(7)
 
 _vp, _i, _u, _sz, _ll = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint, ctypes.c_size_t, ctypes.c_longlong
@@ -33,6 +35,7 @@ SIGNATURES = {
     "msda_ms_deform_attn_backward": (_i, [_vp] * 9 + [_vp, _sz] + [_i] * 7 + [_i, _i, _u, _vp]),
     "msda_fused_forward": (_i, [_vp] * 7 + [_i] * 8 + [_i, _i, _u, _vp]),
     "msda_fused_backward": (_i, [_vp] * 11 + [_vp, _sz] + [_i] * 8 + [_i, _i, _u, _vp]),
+    "msda_fused_backward_bf16_static": (_i, [_vp] * 11 + [_i] * 8 + [_i, _u, _vp]),
     "msda_sample_forward": (_i, [_vp] * 5 + [_i] * 7 + [_i, _i, _u, _vp]),
     "msda_sample_backward": (_i, [_vp] * 7 + [_vp, _sz] + [_i] * 7 + [_i, _i, _u, _vp]),
     "msda_cap_sample_forward": (_i, [_vp] * 6 + [_i] * 8 + [_i, _i, _u, _vp]),

@@ -7,6 +7,7 @@
 // back as return codes.
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 
 #include "msda_fast.cuh"
 #include "msda_generic.cuh"
@@ -479,6 +480,8 @@ const char *msda_error_string(int code)
         case MSDA_ERR_WORKSPACE: return "msda: workspace too small (see msda_backward_workspace_bytes)";
         case MSDA_ERR_PAD: return "msda: unknown pad_mode";
         case MSDA_ERR_UNSUPPORTED: return "msda: combination not supported";
+        case MSDA_ERR_STATIC_SCRATCH:
+            return "msda: N*S*M*D*4 exceeds MSDA_STATIC_SCRATCH_BYTES (use msda_fused_backward with a workspace)";
         default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "msda: unknown error";
     }
 }
@@ -979,3 +982,53 @@ int msda_sample_backward(const void *value, const int64_t *spatial_shapes, const
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// msda_fused_backward_bf16_static: the bf16 fused backward with its fp32 accumulation image in a static device array.
+// No counterpart in the reference (see include/msda.h).  In host code `g_static_scratch` is only a handle for the runtime's
+// symbol table, not a device address: the address each device maps it to comes from cudaGetSymbolAddress, asked once per
+// device with that device current, and that pointer is what the kernels receive.
+// ---------------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_static_scratch[MSDA_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mutex;
+float *g_scratch_ptr[kMaxDevices];   // [device ordinal] -> device address of g_static_scratch there (NULL: not resolved yet)
+
+int static_scratch(float **out)
+{
+    int dev = -1;
+    if (cudaError_t e = cudaGetDevice(&dev)) return (int)e;
+    if (dev < 0 || dev >= kMaxDevices) return MSDA_ERR_UNSUPPORTED;
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);
+    if (!g_scratch_ptr[dev]) {
+        void *p = nullptr;
+        if (cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch)) return (int)e;
+        if (!p || !aligned16(p)) return MSDA_ERR_ALIGN;
+        g_scratch_ptr[dev] = static_cast<float *>(p);
+    }
+    *out = g_scratch_ptr[dev];
+    return MSDA_OK;
+}
+
+}  // namespace
+
+extern "C" int msda_fused_backward_bf16_static(const void *value, const int64_t *temporal_shapes,
+                                               const int64_t *level_start_index, const float *reference_points,
+                                               const float *sampling_offsets, const float *attn_logits,
+                                               const void *grad_output, void *grad_value, float *grad_reference_points,
+                                               float *grad_sampling_offsets, float *grad_attn_logits, int N, int S, int M,
+                                               int D, int L, int Lq, int P, int R, int pad_mode, unsigned flags, void *stream)
+{
+    g_launches = 0; g_path = MSDA_PATH_NONE;
+    if (int e = check_dims(Dims{N, S, M, D, L, Lq, P}, MSDA_BF16, pad_mode)) return e;
+    if ((unsigned long long)N * S * M * D * sizeof(float) > MSDA_STATIC_SCRATCH_BYTES) return MSDA_ERR_STATIC_SCRATCH;
+    float *scratch = nullptr;
+    if (int e = static_scratch(&scratch)) return e;
+    // the shared path zero-fills the N*S*M*D floats it accumulates into on `stream` first: what an earlier call left is gone
+    return msda_fused_backward(value, temporal_shapes, level_start_index, reference_points, sampling_offsets, attn_logits,
+                               grad_output, grad_value, grad_reference_points, grad_sampling_offsets, grad_attn_logits,
+                               scratch, MSDA_STATIC_SCRATCH_BYTES, N, S, M, D, L, Lq, P, R, MSDA_BF16, pad_mode, flags, stream);
+}

@@ -68,7 +68,8 @@ enum {
     MSDA_ERR_ALIGN = -4,      /* a base pointer is not 16-byte aligned */
     MSDA_ERR_WORKSPACE = -5,  /* workspace smaller than msda_backward_workspace_bytes() */
     MSDA_ERR_PAD = -6,        /* unknown pad_mode */
-    MSDA_ERR_UNSUPPORTED = -7 /* combination not implemented (e.g. 2-D shapes with bf16 fast path) */
+    MSDA_ERR_UNSUPPORTED = -7,/* combination not implemented (e.g. 2-D shapes with bf16 fast path) */
+    MSDA_ERR_STATIC_SCRATCH = -8 /* msda_fused_backward_bf16_static: N*S*M*D*4 > MSDA_STATIC_SCRATCH_BYTES */
 };
 
 #define MSDA_MAX_LEVELS 32
@@ -146,6 +147,30 @@ int msda_fused_backward(const void *value, const int64_t *temporal_shapes,
                         float *grad_sampling_offsets, float *grad_attn_logits, void *workspace,
                         size_t workspace_bytes, int N, int S, int M, int D, int L, int Lq, int P,
                         int R, int dtype, int pad_mode, unsigned flags, void *stream);
+
+/* msda_fused_backward for bf16 values WITHOUT a caller-provided workspace and without any allocation.
+ * No counterpart in the reference: added for callers
+ * that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  The fp32 accumulation image of grad_value that the bf16 backward needs lives in a
+ * file-scope __device__ array of MSDA_STATIC_SCRATCH_BYTES (16 MiB) inside the library; every GPU that
+ * loads the library holds that much until the process exits.
+ *   - arguments and results as msda_fused_backward with dtype = MSDA_BF16 (value, grad_output,
+ *     grad_value bf16; everything else f32); inputs and outputs are still the caller's buffers;
+ *   - N*S*M*D*4 > MSDA_STATIC_SCRATCH_BYTES returns MSDA_ERR_STATIC_SCRATCH and launches nothing
+ *     (N*S*M*D <= 4 194 304: e.g. 16 videos of the YouCook2 encoder memory, S = 375, M*D = 512);
+ *   - calls no cudaMalloc / cudaFree / allocating library routine.  The first call on a device
+ *     resolves the array's device address (cudaGetSymbolAddress, that device current) and caches it;
+ *   - the array is shared by every call on the device and keeps the previous call's contents: each
+ *     call zero-fills the part it uses on `stream` before its kernels.  Calls that overlap on the
+ *     GPU (different streams, no ordering between them) race on it -- serialise them. */
+#define MSDA_STATIC_SCRATCH_BYTES (16u << 20)
+int msda_fused_backward_bf16_static(const void *value, const int64_t *temporal_shapes,
+                                    const int64_t *level_start_index, const float *reference_points,
+                                    const float *sampling_offsets, const float *attn_logits,
+                                    const void *grad_output, void *grad_value,
+                                    float *grad_reference_points, float *grad_sampling_offsets,
+                                    float *grad_attn_logits, int N, int S, int M, int D, int L, int Lq,
+                                    int P, int R, int pad_mode, unsigned flags, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Sampler: the return_value=True branch of ms_deform_attn_core_pytorch
