@@ -19,7 +19,8 @@ PAD_BORDER, PAD_ZEROS = 0, 1
 FLAG_ASSUME_1D, FLAG_FORCE_GENERIC, FLAG_NO_SMALL = 1, 2, 4
 STATIC_SCRATCH_BYTES = 16 << 20    # MSDA_STATIC_SCRATCH_BYTES
 ERR_STATIC_SCRATCH = -8
-PATH_NONE, PATH_LEAN, PATH_TILE, PATH_FAST, PATH_GENERIC, PATH_SMALL, PATH_PROJ = range(7)
+PATH_NONE, PATH_LEAN, PATH_TILE, PATH_FAST, PATH_GENERIC, PATH_SMALL, PATH_PROJ, PATH_MATCH = range(8)
+LSAP_MAX_DIM = 1024
 
 _vp, _i, _u, _sz, _ll = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint, ctypes.c_size_t, ctypes.c_longlong
 
@@ -48,6 +49,7 @@ SIGNATURES = {
     "msda_proj_forward": (_i, [_vp] * 8 + [_i] * 5 + [_vp]),
     "msda_proj_dgrad": (_i, [_vp] * 6 + [_i] * 5 + [_vp]),
     "msda_proj_wgrad": (_i, [_vp] * 8 + [_i] * 5 + [_vp]),
+    "msda_lsap_f32": (_i, [_vp] * 4 + [_i] * 3 + [_vp]),
 }
 
 _lib = None

@@ -5,7 +5,10 @@ execution is bound by launch overhead (68 ms/step).  The only point where the ho
 Hungarian assignment (scipy, pdvc/matcher.py:115-117).  So the step is split there:
 
     stage 1  (graph)  features -> pyramid -> encoder -> decoder -> heads -> matching cost matrices of all layers
+                      [-> Hungarian matching of all layers on the device, csrc/msda_match.cuh: `device_match`]
     host              ONE read-back of the cost matrices, linear_sum_assignment per layer, indices uploaded
+                      [skipped with `device_match`: the indices are static outputs of stage 1's graph and the host
+                       never waits for the device inside a step]
     stage 2  (graph)  set losses with the matched indices + the teacher-forced caption LSTM loops -> total loss
 
 Each stage is captured once per shape key by `graph_module` below (forward graph + backward graph; the MSDeformAttn /
@@ -27,6 +30,7 @@ import torch
 from scipy.optimize import linear_sum_assignment
 from torch import nn
 
+from ..ops.functions.matching import linear_sum_assignment_cuda, lsap_supported
 from .model import caption_steps
 
 
@@ -146,6 +150,7 @@ def graph_module(module, sample_args, warmup=3, autocast=None, grad_sinks=None):
 
 
 ALIAS_STAGE_INPUTS = True     # stage 2 reads stage 1's static output buffers directly
+LSAP_MAX_DIM = 1024           # largest cost matrix side msda_lsap_f32 takes (include/msda.h)
 
 LOSS_TERMS = ("loss_ce", "loss_counter", "loss_bbox", "loss_giou", "loss_self_iou", "cardinality_error", "loss_caption")
 
@@ -161,6 +166,7 @@ class FeatureStage(nn.Module):
         self.class_head, self.count_head, self.bbox_head = model.class_head, model.count_head, model.bbox_head
         self.__dict__["_model"] = model          # not registered: parameters are exposed through the members above
         self.__dict__["_matcher"] = matcher
+        self.device_match = False                # set per call by StagedStep: assignment computed here, on the device
 
     def forward(self, vf, valid_mask, duration, tgt_boxes, tgt_labels):
         model = self._model
@@ -169,8 +175,12 @@ class FeatureStage(nn.Module):
         with torch.no_grad():
             costs = torch.stack([self._matcher.cost_matrix(logits[l], boxes[l], tgt_labels, tgt_boxes)
                                  for l in range(hs.shape[0])])
-        return (hs, init_reference, inter_references, logits, counts, boxes, others['memory'], others['mask_flatten'],
+        outs = (hs, init_reference, inter_references, logits, counts, boxes, others['memory'], others['mask_flatten'],
                 others['valid_ratios'], costs)
+        if self.device_match:
+            # one video per step: cost_matrix returns (Q, G) per layer -> (layers, Q, G); rows ascending = matcher.py:115
+            outs = outs + linear_sum_assignment_cuda(costs)
+        return outs
 
 
 class LossStage(nn.Module):
@@ -295,14 +305,19 @@ class LossStage(nn.Module):
 
 
 class StagedStep(nn.Module):
-    """forward(dt) -> (total loss, dict of loss terms) for ONE video, as stage 1 -> host matching -> stage 2."""
+    """forward(dt) -> (total loss, dict of loss terms, (query indices, event indices) per layer) for ONE video, as
+    stage 1 -> matching -> stage 2.  The indices are device tensors with `device_match` (default on CUDA), else the host
+    arrays scipy returned."""
 
-    def __init__(self, model, criterion, graphs=True, amp=False, max_graphs=64):
+    def __init__(self, model, criterion, graphs=True, amp=False, max_graphs=64, device_match=True):
         super().__init__()
         self.model = model
         self.criterion = criterion
         self.graphs = graphs
         self.amp = amp
+        # Hungarian matching on the device (CUDA only; needs events <= queries <= 1024, else the host path below):
+        # no device->host read-back inside the step, the host runs ahead of the GPU
+        self.device_match = device_match
         self.max_graphs = max_graphs      # stage-2 graphs kept (one per shape key, least recently used dropped first)
         # Trainer(sync="overlap"): {id(param): flat-bucket view} and one callback per stage (see graph_module)
         self.__dict__["grad_sinks"] = None
@@ -369,23 +384,35 @@ class StagedStep(nn.Module):
         target = dt['video_target'][0]
         args1 = (vf, valid, duration, target['boxes'], target['labels'])
         use_graphs = self.graphs and vf.is_cuda
+        n_gt, n_query = int(target['boxes'].shape[0]), int(self.model.cfg.num_queries)
+        # every event is matched when there are at least as many queries, so the word-step count (the one host decision
+        # that depends on WHICH captions were matched) is known without the assignment
+        on_device = bool(self.device_match and vf.is_cuda and 1 <= n_gt <= n_query <= LSAP_MAX_DIM)
         stage1 = self.stage1
+        stage1.device_match = on_device
         if use_graphs:      # the matching costs are part of stage 1, so its graph depends on the event count too
-            key1 = (int(vf.shape[1]), int(target['boxes'].shape[0]))
+            key1 = (int(vf.shape[1]), n_gt, on_device)
             stage1 = self._cached(self._stage1, key1, lambda: self._graph(self.stage1, tuple(a.detach().clone() for a in args1), 1))
         # the event count is host data: its all-reduce (criterion.py:169-171) is issued before stage 1 and has long
         # finished when stage 2 reads it, instead of making the ranks meet in the middle of the step
         num_boxes = self._num_boxes(int(target['boxes'].shape[0]), vf.device)
-        hs, init_ref, inter_refs, logits, counts, boxes, memory, mask_flat, valid_ratios, costs = stage1(*args1)
+        outs = stage1(*args1)
+        hs, init_ref, inter_refs, logits, counts, boxes, memory, mask_flat, valid_ratios, costs = outs[:10]
         n_pred = hs.shape[0]
-        q_host, t_host = self._match(costs, n_pred)
         cap_host = dt.get('cap_tensor_host')
         cap_host = dt['cap_tensor'].cpu().numpy() if cap_host is None else np.asarray(cap_host)
-        n_steps = tuple(caption_steps(cap_host[t_host[lid]]) for lid in range(n_pred))
-        q_idx, t_idx = self._upload_indices(q_host, t_host, vf.device)
+        if on_device:
+            q_idx, t_idx = outs[10], outs[11]
+            n_steps = (caption_steps(cap_host[:n_gt]),) * n_pred
+            matched = (q_idx, t_idx)
+        else:
+            q_host, t_host = self._match(costs, n_pred)
+            n_steps = tuple(caption_steps(cap_host[t_host[lid]]) for lid in range(n_pred))
+            q_idx, t_idx = self._upload_indices(q_host, t_host, vf.device)
+            matched = (q_host, t_host)
         args2 = (hs, init_ref, inter_refs.detach(), logits, counts, boxes, memory, mask_flat, valid_ratios.detach(),
                  target['boxes'], target['labels'], dt['cap_tensor'], dt['cap_mask'], num_boxes, q_idx, t_idx)
-        key = (int(target['boxes'].shape[0]), q_host.shape[1], n_steps, int(vf.shape[1]), int(dt['cap_tensor'].shape[1]))
+        key = (n_gt, int(q_idx.shape[1]), n_steps, int(vf.shape[1]), int(dt['cap_tensor'].shape[1]), on_device)
 
         def make_stage2():
             lengths = pyramid_lengths(vf.shape[1], self.model.cfg.num_feature_levels)
@@ -393,11 +420,13 @@ class StagedStep(nn.Module):
             if use_graphs:
                 # the first 9 arguments are static outputs of the stage-1 graph: captured in place (same storage), so the
                 # replay wrapper finds identical addresses and skips its input copies; everything else is cloned
-                sample = tuple((a.detach() if (ALIAS_STAGE_INPUTS and i < 9) else a.detach().clone()).requires_grad_(a.requires_grad)
+                # (with device matching the two index tensors, arguments 14 and 15, are static stage-1 outputs as well)
+                static = lambda i: ALIAS_STAGE_INPUTS and (i < 9 or (on_device and i >= 14))  # noqa: E731
+                sample = tuple((a.detach() if static(i) else a.detach().clone()).requires_grad_(a.requires_grad)
                                for i, a in enumerate(args2))
                 stage2 = self._graph(stage2, sample, 2)
             return stage2
 
         total, terms = self._cached(self._stage2, key, make_stage2)(*args2)
         names = [name + ('' if lid == n_pred - 1 else f'_{lid}') for lid in range(n_pred) for name in LOSS_TERMS]
-        return total, dict(zip(names, terms.unbind(0))), (q_host, t_host)
+        return total, dict(zip(names, terms.unbind(0))), matched

@@ -287,6 +287,25 @@ int msda_proj_wgrad(const void *dy0, const void *dy1, const void *x, const unsig
                     float *dw0, float *db0, float *dw1, float *db1, int rows, int K, int N0, int N1,
                     int dtype, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Hungarian matching of the set-prediction loss on the device: replaces the host round
+ * trip of pdvc/matcher.py:113-117 -- `C.view(bs, num_queries, -1).cpu()` followed by
+ * scipy.optimize.linear_sum_assignment per cost matrix -- the one point of a PDVC training step where
+ * the host waits for the device.
+ *   cost      (B, R, C) f32, device   B independent matrices (decoder layers); R queries, C events
+ *   row_idx   (B, min(R,C)) int64     matched rows in ascending order   (scipy's row_ind)
+ *   col_idx   (B, min(R,C)) int64     their columns                      (scipy's col_ind)
+ *   status    (B) int32 or NULL       0 ok; 1 a NaN or -inf entry; 2 infeasible (a row with only +inf) --
+ *                                     scipy raises ValueError for both; here the pairing written is the
+ *                                     identity and the caller reads the flag when it next synchronises.
+ * Same algorithm, arithmetic (float64 duals), scan order and tie rule as scipy's rectangular_lsap, so
+ * the assignment is scipy's also when costs tie.  max(R, C) <= 1024, else MSDA_ERR_UNSUPPORTED (the
+ * Python wrapper then takes the host path).  One warp per matrix; enqueued on `stream`, no
+ * synchronisation, graph-capturable.
+ * ------------------------------------------------------------------------------------------- */
+int msda_lsap_f32(const float *cost, long long *row_idx, long long *col_idx, int *status, int B, int R,
+                  int C, void *stream);
+
 /* Diagnostics (the library's only state: two thread-local integers, reset by every entry point).
  * msda_last_launch_count: number of kernels / memsets the last call on this thread enqueued (bench.py's
  * gpu_launches).  msda_last_launch_path: which kernel family served the last MSDeformAttn call -- the tests use it
@@ -298,7 +317,8 @@ enum {
     MSDA_PATH_FAST = 3,    /* csrc/msda_fast.cuh: any 16-byte divisible D */
     MSDA_PATH_GENERIC = 4, /* csrc/msda_generic.cuh: any D, 2-D levels, f64, sampler */
     MSDA_PATH_SMALL = 5,   /* csrc/msda_small.cuh: single-phase kernels for launch-latency-bound problems */
-    MSDA_PATH_PROJ = 6     /* csrc/msda_proj.cuh: tcgen05 projection GEMMs */
+    MSDA_PATH_PROJ = 6,    /* csrc/msda_proj.cuh: tcgen05 projection GEMMs */
+    MSDA_PATH_MATCH = 7    /* csrc/msda_match.cuh: linear sum assignment */
 };
 int msda_last_launch_count(void);
 int msda_last_launch_path(void);
