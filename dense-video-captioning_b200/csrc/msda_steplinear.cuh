@@ -14,6 +14,7 @@
 // by the caller); the weight gradient is deferred to one GEMM over all word steps (pdvc/step_linear.py).
 #pragma once
 #include "msda_common.cuh"
+#include "msda_tile.cuh"   // reduce_nv
 
 namespace msda {
 
@@ -63,28 +64,29 @@ msda_skinny_linear_kernel(const float *__restrict__ x, const float *__restrict__
             }
         }
     }
-    // butterfly over the 32 lanes; lane (r*NW + j) keeps sum (r, j)
-    float mine = 0.f;
+    // sum over the 32 lanes with the transposing butterfly (31 shuffles for 32 sums instead of 5 each: this kernel runs as
+    // one wave of ~28 warps per SM and the shuffle pipe, one warp instruction per clock and SM, was a fifth of its time);
+    // lane l ends up with the total of sum number l / (32 / OUT), numbered r * NW + j
+    float flat[OUT];
 #pragma unroll
     for (int r = 0; r < kSkinnyRows; ++r)
 #pragma unroll
-        for (int j = 0; j < kSkinnyNW; ++j) {
-            float v = acc[r][j];
-#pragma unroll
-            for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
-            if (lane == r * kSkinnyNW + j) mine = v;
-        }
+        for (int j = 0; j < kSkinnyNW; ++j) flat[r * kSkinnyNW + j] = acc[r][j];
+    reduce_nv<32, OUT>(flat, lane);
+    constexpr int LPV = 32 / OUT;            // lanes that hold the same total
+    const int vidx = lane / LPV;
+    const bool writer = lane % LPV == 0;
+    float mine = flat[0];
     if (KS > 1) {
-        if (lane < OUT) part[group][slice][lane] = mine;
+        if (writer) part[group][slice][vidx] = mine;
         __syncthreads();
         if (slice != 0) return;
         mine = 0.f;
-        if (lane < OUT)
 #pragma unroll
-            for (int s = 0; s < KS; ++s) mine += part[group][s][lane];
+        for (int s = 0; s < KS; ++s) mine += part[group][s][vidx];
     }
-    const int r = lane / kSkinnyNW, j = lane % kSkinnyNW;
-    if (lane < OUT && r < rows && n0 + j < N)
+    const int r = vidx / kSkinnyNW, j = vidx % kSkinnyNW;
+    if (writer && r < rows && n0 + j < N)
         y[(long long)(m0 + r) * N + n0 + j] = mine + (bias ? __ldg(bias + n0 + j) : 0.f);
 }
 

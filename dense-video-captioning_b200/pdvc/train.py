@@ -83,14 +83,20 @@ def input_bytes(host):
     return sum(v.numel() * v.element_size() for v in host.values())
 
 
+FLAT_OPTIMIZER = True     # default of Trainer(flat_optimizer=None); module-level so tools/pdvc_ab.py can A/B it
+
+
 class Trainer:
     """model + criterion + Adam(lr 5e-5, wd 1e-4) + grad clip 100 (cfgs/anet_c3d_pdvcl.yml:17,21; opts.py:104-105)."""
 
     def __init__(self, name_or_cfg, device, world_size=1, lr=5e-5, weight_decay=1e-4, grad_clip=100.0, amp=None,
-                 seed=0, dropout=None, mode="graphs", sync="overlap"):
-        """mode: 'graphs' = two CUDA graphs around the host matcher (pdvc/graphed.py; CUDA only), 'staged' = the same
-        two stages eagerly, 'eager' = the reference's control flow (model.forward with the criterion inside).
-        sync (world_size > 1): 'overlap' | 'flat' | 'ddp', see the module docstring."""
+                 seed=0, dropout=None, mode="graphs", sync="overlap", flat_optimizer=None):
+        """mode: 'graphs' = two CUDA graphs with the Hungarian matching on the device between them (pdvc/graphed.py; CUDA
+        only), 'staged' = the same two stages eagerly, 'eager' = the reference's control flow (model.forward with the
+        criterion inside).
+        sync (world_size > 1): 'overlap' | 'flat' | 'ddp', see the module docstring.
+        flat_optimizer: clip + Adam as two launches over the flat gradient buckets (pdvc/optim.py) where those exist
+        (mode 'graphs' with sync 'overlap'); otherwise torch's clip_grad_norm_ + fused Adam."""
         if sync not in ("overlap", "flat", "ddp"):
             raise ValueError(f"sync must be 'overlap', 'flat' or 'ddp', got {sync!r}")
         spec = CONFIGS[name_or_cfg] if isinstance(name_or_cfg, str) else dict(cfg=name_or_cfg, n_gt=4, cap_len=12, amp=False)
@@ -144,9 +150,15 @@ class Trainer:
                 torch.cuda.current_stream().wait_stream(side)
             else:
                 self.net = DDP(self.net, gradient_as_bucket_view=True, broadcast_buffers=False)
-        # same update rule as the reference's torch.optim.Adam (train.py:100-104); on CUDA the single-kernel (fused) variant
-        self.optimizer = torch.optim.Adam(self.params, lr=lr, weight_decay=weight_decay,
-                                          fused=(self.device.type == "cuda"))
+        # same update rule as the reference's torch.optim.Adam (train.py:123) after clip_grad_norm_ (train.py:185)
+        flat_optimizer = FLAT_OPTIMIZER if flat_optimizer is None else flat_optimizer
+        self._flat_optimizer = bool(flat_optimizer and self._sinks_live and self.device.type == "cuda")
+        if self._flat_optimizer:
+            from .optim import FlatClipAdam
+            self.optimizer = FlatClipAdam(self._buckets, lr=lr, weight_decay=weight_decay, max_norm=grad_clip, order=self.params)
+        else:
+            self.optimizer = torch.optim.Adam(self.params, lr=lr, weight_decay=weight_decay,
+                                              fused=(self.device.type == "cuda"))
         self.grad_clip = grad_clip
         self.weight_dict = self.criterion.weight_dict
 
@@ -177,8 +189,11 @@ class Trainer:
             self._allreduce_buckets_after_backward()
         elif self.world_size > 1 and self.sync in ("flat", "overlap"):
             self._allreduce_gradients()
-        torch.nn.utils.clip_grad_norm_(self.params, self.grad_clip)
-        self.optimizer.step()
+        if self._flat_optimizer:
+            self.optimizer.step()                    # global-norm clipping included
+        else:
+            torch.nn.utils.clip_grad_norm_(self.params, self.grad_clip)
+            self.optimizer.step()
         self.last_losses = losses
         return total.detach().clone()
 

@@ -306,6 +306,31 @@ int msda_proj_wgrad(const void *dy0, const void *dy1, const void *x, const unsig
 int msda_lsap_f32(const float *cost, long long *row_idx, long long *col_idx, int *status, int B, int R,
                   int C, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Gradient-norm clipping + Adam in two launches: replaces
+ * `torch.nn.utils.clip_grad_norm_(model.parameters(), opt.grad_clip)` + `optimizer.step()` of
+ * torch.optim.Adam(lr, weight_decay) at the end of the reference's step (train.py:185-187, :123) for a
+ * trainer that keeps its gradients in flat buckets.
+ *   segments  device array of n_segments { const float *grad; int64 count }   (16 bytes each): the
+ *             buckets whose global L2 norm is clipped to max_norm (max_norm <= 0: no clipping,
+ *             segments / partials unused)
+ *   chunks    device array of n_chunks { float *param; const float *grad; float *exp_avg;
+ *             float *exp_avg_sq; int32 count; int32 pad }                      (40 bytes each): runs of
+ *             one parameter tensor, any length (8192 balances the blocks)
+ *   partials  device scratch of partials_capacity floats (>= 1; 1024 is always enough)
+ *   norm_out  device float or NULL: receives the total gradient norm (what clip_grad_norm_ returns)
+ *   step      t >= 1, the number of this update (bias corrections 1 - beta^t)
+ * Update rule (torch's fused Adam, fp32): g = coef*grad + weight_decay*p; m = lerp(m, g, 1-beta1);
+ * v = beta2*v + (1-beta2)*g*g; p -= lr/(1-beta1^t) * m / (sqrt(v)/sqrt(1-beta2^t) + eps), with
+ * coef = min(1, max_norm / (norm + 1e-6)).  The hyper-parameters are doubles: 1-beta and the bias
+ * corrections are formed in double precision and rounded once, as torch does.  The gradients are read,
+ * not rescaled in place.
+ * ------------------------------------------------------------------------------------------- */
+int msda_adam_clip_step(const void *segments, int n_segments, const void *chunks, int n_chunks,
+                        float *partials, int partials_capacity, float *norm_out, double lr,
+                        double beta1, double beta2, double eps, double weight_decay, int step,
+                        double max_norm, void *stream);
+
 /* Diagnostics (the library's only state: two thread-local integers, reset by every entry point).
  * msda_last_launch_count: number of kernels / memsets the last call on this thread enqueued (bench.py's
  * gpu_launches).  msda_last_launch_path: which kernel family served the last MSDeformAttn call -- the tests use it
