@@ -50,6 +50,7 @@ SIGNATURES = {
     "msda_proj_dgrad": (_i, [_vp] * 6 + [_i] * 5 + [_vp]),
     "msda_proj_wgrad": (_i, [_vp] * 8 + [_i] * 5 + [_vp]),
     "msda_lsap_f32": (_i, [_vp] * 4 + [_i] * 3 + [_vp]),
+    "msda_pdvc_match_f32": (_i, [_vp] * 8 + [_i] * 4 + [ctypes.c_double] * 5 + [_vp]),
     "msda_adam_clip_step": (_i, [_vp, _i, _vp, _i, _vp, _i, _vp] + [ctypes.c_double] * 5 + [_i, ctypes.c_double, _vp]),
 }
 

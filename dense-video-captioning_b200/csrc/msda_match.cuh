@@ -25,7 +25,7 @@ constexpr int kMaxDim = 1024;              // max(rows, cols) of a cost matrix
 constexpr unsigned kFullMask = 0xffffffffu;
 
 struct Args {
-    const float *cost;       // (B, R, C) row-major
+    float *cost;             // (B, R, C) row-major: read (PlainCost) or written first (PdvcCost)
     long long *row_idx;      // (B, min(R, C)) ascending rows
     long long *col_idx;      // (B, min(R, C)) their columns
     int *status;             // (B) 0 ok, 1 invalid entries (NaN / -inf), 2 infeasible; may be NULL
@@ -58,16 +58,63 @@ __device__ __forceinline__ bool better(const Cand &a, const Cand &b)   // a stri
     return a.val < b.val || (a.val == b.val && a.rank > b.rank);
 }
 
+// ---- where the costs come from ----------------------------------------------------------------------------------------
+struct PlainCost {                                   // the caller's matrix
+    __device__ __forceinline__ float operator()(const float *cost, int b, int k, int r, int c) const { return cost[k]; }
+    static constexpr bool kWrites = false;
+};
+
+// The matching cost of PDVC's set-prediction loss, pdvc/matcher.py:84-103, for one (query r, event c) of decoder layer b:
+//     cost_class * (focal_pos - focal_neg)(sigmoid(logit[r, label_c])) + cost_bbox * L1((centre, length)) - cost_giou * GIoU
+// evaluated operation by operation in float32 as the reference's tensor expression is (no fused multiply-adds, the same
+// expf / logf), so that the matrix -- and with it the assignment -- is the one the torch ops produce.
+struct PdvcCost {
+    const float *logits;      // (B, R, n_classes)
+    const float *boxes;       // (B, R, 2) centre, length
+    const long long *labels;  // (C)
+    const float *tgt_boxes;   // (C, 2)
+    int n_classes, R;
+    float w_class, w_bbox, w_giou, alpha, one_minus_alpha, gamma;    // 1 - alpha formed in double by the host, like Python does
+    static constexpr bool kWrites = true;
+
+    __device__ __forceinline__ float focal_pow(float x) const { return gamma == 2.f ? __fmul_rn(x, x) : powf(x, gamma); }
+
+    __device__ __forceinline__ float operator()(const float *, int b, int, int r, int c) const
+    {
+        const float logit = logits[((size_t)b * R + r) * n_classes + (int)labels[c]];
+        const float prob = 1.f / (1.f + expf(-logit));
+        // neg = (1 - alpha) * prob^gamma * -log(1 - prob + 1e-8);  pos = alpha * (1 - prob)^gamma * -log(prob + 1e-8)
+        const float neg = __fmul_rn(__fmul_rn(one_minus_alpha, focal_pow(prob)), -logf(__fadd_rn(__fsub_rn(1.f, prob), 1e-8f)));
+        const float pos = __fmul_rn(__fmul_rn(alpha, focal_pow(__fsub_rn(1.f, prob))), -logf(__fadd_rn(prob, 1e-8f)));
+        float cost = __fmul_rn(w_class, __fsub_rn(pos, neg));
+        const float qc = boxes[((size_t)b * R + r) * 2], ql = boxes[((size_t)b * R + r) * 2 + 1];
+        const float tc = tgt_boxes[2 * c], tl = tgt_boxes[2 * c + 1];
+        const float l1 = __fadd_rn(fabsf(__fsub_rn(qc, tc)), fabsf(__fsub_rn(ql, tl)));          // torch.cdist(p=1)
+        cost = __fadd_rn(cost, __fmul_rn(w_bbox, l1));
+        // (centre, length) -> (start, end); 1-D generalised IoU (misc/detr_utils/box_ops.py:8-48)
+        const float a0 = __fsub_rn(qc, __fmul_rn(0.5f, ql)), a1 = __fadd_rn(qc, __fmul_rn(0.5f, ql));
+        const float b0 = __fsub_rn(tc, __fmul_rn(0.5f, tl)), b1 = __fadd_rn(tc, __fmul_rn(0.5f, tl));
+        const float len_a = __fsub_rn(a1, a0), len_b = __fsub_rn(b1, b0);
+        const float inter = fmaxf(__fsub_rn(fminf(a1, b1), fmaxf(a0, b0)), 0.f);
+        const float uni = __fsub_rn(__fadd_rn(len_a, len_b), inter);
+        const float iou = __fdiv_rn(inter, __fadd_rn(uni, 1e-5f));
+        const float hull = fmaxf(__fsub_rn(fmaxf(a1, b1), fminf(a0, b0)), 0.f);
+        const float giou = __fsub_rn(iou, __fdiv_rn(__fsub_rn(hull, uni), __fadd_rn(hull, 1e-5f)));
+        return __fsub_rn(cost, __fmul_rn(w_giou, giou));
+    }
+};
+
 constexpr int kScanBatch = 4;   // columns per lane whose loads are issued together (the scan is a chain of shared-memory round trips)
 
-__global__ void __launch_bounds__(32) msda_lsap_kernel(const Args a)
+template <class Source>
+__global__ void __launch_bounds__(32) msda_lsap_kernel(const Args a, const Source source)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x;
     const int b = blockIdx.x;
     const bool transposed = a.C < a.R;               // scipy: solve the transposed problem when there are fewer columns
     const int nr = transposed ? a.C : a.R, nc = transposed ? a.R : a.C;
-    const float *cost = a.cost + (size_t)b * a.R * a.C;
+    float *cost = a.cost + (size_t)b * a.R * a.C;
     long long *row_idx = a.row_idx + (size_t)b * nr, *col_idx = a.col_idx + (size_t)b * nr;
 
     double *sp = reinterpret_cast<double *>(smem);   // shortest path cost to each column
@@ -84,14 +131,14 @@ __global__ void __launch_bounds__(32) msda_lsap_kernel(const Args a)
     // ---- stage + validate ----
     int invalid = 0;
     for (int k = lane; k < a.R * a.C; k += 32) {
-        const float c = cost[k];
+        const int r = k / a.C, q = k - r * a.C;
+        const float c = source(cost, b, k, r, q);
+        if (Source::kWrites) cost[k] = c;
         invalid |= (c != c) || (c == -CUDART_INF_F);
-        if (a.staged) {
-            const int r = k / a.C, q = k - r * a.C;
-            cs[transposed ? q * nc + r : k] = c;
-        }
+        if (a.staged) cs[transposed ? q * nc + r : k] = c;
     }
     invalid = __any_sync(kFullMask, invalid);
+    if (Source::kWrites) __threadfence_block();       // an unstaged search reads the matrix back from global memory
     for (int j = lane; j < nc; j += 32) { v[j] = 0.0; row4col[j] = -1; }
     for (int i = lane; i < nr; i += 32) { u[i] = 0.0; col4row[i] = -1; }
     __syncwarp();

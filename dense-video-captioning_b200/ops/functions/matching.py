@@ -33,3 +33,32 @@ def linear_sum_assignment_cuda(costs, status=None):
                                       torch.cuda.current_stream(costs.device).cuda_stream)
     _lib.check(rc, "msda_lsap_f32")
     return rows, cols
+
+
+def pdvc_match_cuda(pred_logits, pred_boxes, tgt_labels, tgt_boxes, cost_class, cost_bbox, cost_giou, alpha, gamma):
+    """HungarianMatcher.forward of one video for all decoder layers in one launch (pdvc/matcher.py:71-117).
+    pred_logits (layers, queries, classes), pred_boxes (layers, queries, 2), float32 on the device; tgt_labels (targets,)
+    int64, tgt_boxes (targets, 2).  Returns (cost (layers, queries, targets) float32, query_idx, target_idx (layers,
+    min(queries, targets)) int64): the cost matrix of matcher.py:84-103 and scipy's assignment on it."""
+    for t in (pred_logits, pred_boxes, tgt_labels, tgt_boxes):
+        if not t.is_cuda:
+            raise RuntimeError("pdvc_match_cuda: tensors must be on a CUDA device (no CPU fallback)")
+    if pred_logits.dtype != torch.float32 or pred_boxes.dtype != torch.float32:
+        raise ValueError("pdvc_match_cuda takes float32 predictions")
+    layers, queries, classes = pred_logits.shape
+    targets = tgt_boxes.shape[0]
+    if tuple(pred_boxes.shape) != (layers, queries, 2) or tgt_labels.numel() != targets or tgt_boxes.shape[-1] != 2:
+        raise ValueError("pdvc_match_cuda: inconsistent shapes")
+    logits, boxes = pred_logits.detach().contiguous(), pred_boxes.detach().contiguous()
+    labels, tboxes = tgt_labels.detach().to(torch.int64).contiguous(), tgt_boxes.detach().to(torch.float32).contiguous()
+    k = min(queries, targets)
+    cost = torch.empty((layers, queries, targets), dtype=torch.float32, device=logits.device)
+    q_idx = torch.empty((layers, k), dtype=torch.int64, device=logits.device)
+    t_idx = torch.empty((layers, k), dtype=torch.int64, device=logits.device)
+    with torch.cuda.device(logits.device):
+        rc = _lib.lib().msda_pdvc_match_f32(logits.data_ptr(), boxes.data_ptr(), labels.data_ptr(), tboxes.data_ptr(),
+                                            cost.data_ptr(), q_idx.data_ptr(), t_idx.data_ptr(), None, layers, queries, classes,
+                                            targets, float(cost_class), float(cost_bbox), float(cost_giou), float(alpha),
+                                            float(gamma), torch.cuda.current_stream(logits.device).cuda_stream)
+    _lib.check(rc, "msda_pdvc_match_f32")
+    return cost, q_idx, t_idx

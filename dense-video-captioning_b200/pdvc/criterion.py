@@ -5,7 +5,8 @@ event-counter loss, L1 + GIoU segment losses.  Restated from pdvc/matcher.py:71-
 One deliberate host-side change: the reference moves one cost matrix per decoder layer to the CPU
 (matcher.py:115, called once per layer from criterion.py:162 and :183); here all layers' matrices go in a single
 transfer, so the step has one device read-back for matching instead of `dec_layers`.  The assignment itself is scipy's
-`linear_sum_assignment` on the host, as in the reference.  The many-to-one assignment the reference also solves
+`linear_sum_assignment` on the host, as in the reference (the two-stage training step, pdvc/graphed.py, runs the same
+algorithm on the device instead: csrc/msda_match.cuh).  The many-to-one assignment the reference also solves
 (matcher.py:118-121) never reaches a loss (criterion.py:49, :103 unpack and drop it) and is not computed.
 """
 import torch

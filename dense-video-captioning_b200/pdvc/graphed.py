@@ -30,7 +30,7 @@ import torch
 from scipy.optimize import linear_sum_assignment
 from torch import nn
 
-from ..ops.functions.matching import linear_sum_assignment_cuda, lsap_supported
+from ..ops.functions.matching import linear_sum_assignment_cuda, pdvc_match_cuda
 from .model import caption_steps
 
 
@@ -151,6 +151,7 @@ def graph_module(module, sample_args, warmup=3, autocast=None, grad_sinks=None):
 
 ALIAS_STAGE_INPUTS = True     # stage 2 reads stage 1's static output buffers directly
 LSAP_MAX_DIM = 1024           # largest cost matrix side msda_lsap_f32 takes (include/msda.h)
+FUSED_MATCH_COST = True       # device matching forms the cost matrices inside the matching kernel (fp32 predictions)
 
 LOSS_TERMS = ("loss_ce", "loss_counter", "loss_bbox", "loss_giou", "loss_self_iou", "cardinality_error", "loss_caption")
 
@@ -172,15 +173,20 @@ class FeatureStage(nn.Module):
         model = self._model
         hs, init_reference, inter_references, others = model.forward_features(vf, valid_mask, duration)
         logits, counts, boxes = model.forward_heads(hs, init_reference, inter_references)
+        matched = ()
         with torch.no_grad():
-            costs = torch.stack([self._matcher.cost_matrix(logits[l], boxes[l], tgt_labels, tgt_boxes)
-                                 for l in range(hs.shape[0])])
-        outs = (hs, init_reference, inter_references, logits, counts, boxes, others['memory'], others['mask_flatten'],
-                others['valid_ratios'], costs)
-        if self.device_match:
-            # one video per step: cost_matrix returns (Q, G) per layer -> (layers, Q, G); rows ascending = matcher.py:115
-            outs = outs + linear_sum_assignment_cuda(costs)
-        return outs
+            m = self._matcher
+            if self.device_match and FUSED_MATCH_COST and logits.dtype == torch.float32 and boxes.dtype == torch.float32:
+                # cost matrices (matcher.py:84-103) and assignment (:115) of all layers in ONE launch; one video per step
+                costs, q_idx, t_idx = pdvc_match_cuda(logits[:, 0], boxes[:, 0], tgt_labels, tgt_boxes, m.cost_class,
+                                                      m.cost_bbox, m.cost_giou, m.cost_alpha, m.cost_gamma)
+                matched = (q_idx, t_idx)
+            else:
+                costs = torch.stack([m.cost_matrix(logits[l], boxes[l], tgt_labels, tgt_boxes) for l in range(hs.shape[0])])
+                if self.device_match:            # (layers, Q, G); rows ascending = matcher.py:115
+                    matched = linear_sum_assignment_cuda(costs)
+        return (hs, init_reference, inter_references, logits, counts, boxes, others['memory'], others['mask_flatten'],
+                others['valid_ratios'], costs) + tuple(matched)
 
 
 class LossStage(nn.Module):

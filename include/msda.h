@@ -306,6 +306,20 @@ int msda_proj_wgrad(const void *dy0, const void *dy1, const void *x, const unsig
 int msda_lsap_f32(const float *cost, long long *row_idx, long long *col_idx, int *status, int B, int R,
                   int C, void *stream);
 
+/* The whole HungarianMatcher.forward of one video (pdvc/matcher.py:71-117) for all decoder layers in one
+ * launch: the cost matrix  cost_class * (focal_pos - focal_neg)(sigmoid(logit)) + cost_bbox * L1 -
+ * cost_giou * GIoU  (matcher.py:84-103; ~45 tensor kernels per layer in the reference) is formed inside
+ * the matching kernel -- each float32 operation as the reference's expression performs it, no
+ * contraction -- written to `cost`, and solved as msda_lsap_f32 does.
+ *   pred_logits (layers, queries, classes) f32     pred_boxes (layers, queries, 2) f32 (centre, length)
+ *   tgt_labels  (targets) int64                     tgt_boxes  (targets, 2) f32
+ *   cost        (layers, queries, targets) f32 out  query_idx / target_idx (layers, min(queries,targets)) int64
+ *   status as msda_lsap_f32.  gamma == 2 is evaluated as x*x (torch's pow fast path). */
+int msda_pdvc_match_f32(const float *pred_logits, const float *pred_boxes, const long long *tgt_labels,
+                        const float *tgt_boxes, float *cost, long long *query_idx, long long *target_idx,
+                        int *status, int layers, int queries, int classes, int targets, double cost_class,
+                        double cost_bbox, double cost_giou, double alpha, double gamma, void *stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Gradient-norm clipping + Adam in two launches: replaces
  * `torch.nn.utils.clip_grad_norm_(model.parameters(), opt.grad_clip)` + `optimizer.step()` of

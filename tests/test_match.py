@@ -163,6 +163,33 @@ def test_kernel_flags_what_scipy_rejects(dvc):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("Q,G,classes,gamma", [(100, 6, 1, 2.0), (100, 30, 1, 2.0), (10, 4, 1, 2.0), (10, 14, 3, 2.0), (50, 9, 2, 1.5)])
+def test_fused_cost_and_matching_against_the_torch_expression(dvc, Q, G, classes, gamma):
+    """msda_pdvc_match_f32 against HungarianMatcher.cost_matrix (the tensor expression of matcher.py:84-103) + scipy: the cost
+    matrix to 2 float32 ulps of its largest entry (each operation is performed in float32 as the expression does; expf / logf /
+    powf may differ from the tensor kernels' in the last place), the assignment exactly."""
+    from dense_video_captioning_b200.ops.functions import pdvc_match_cuda
+    from dense_video_captioning_b200.pdvc.criterion import HungarianMatcher
+    g = torch.Generator().manual_seed(Q * 7 + G)
+    layers = 3
+    logits = (torch.randn(layers, Q, classes, generator=g) * 3).cuda()
+    boxes = torch.stack([torch.rand(layers, Q, generator=g), torch.rand(layers, Q, generator=g) * 0.5 + 0.01], -1).cuda()
+    labels = torch.randint(0, classes, (G,), generator=g).cuda()
+    tboxes = torch.stack([torch.rand(G, generator=g), torch.rand(G, generator=g) * 0.4 + 0.02], -1).cuda()
+    m = HungarianMatcher(cost_class=2.0, cost_bbox=0.0 if Q == 10 else 5.0, cost_giou=4.0, cost_alpha=0.25, cost_gamma=gamma)
+    cost, q_idx, t_idx = pdvc_match_cuda(logits, boxes, labels, tboxes, m.cost_class, m.cost_bbox, m.cost_giou, m.cost_alpha,
+                                         m.cost_gamma)
+    assert dvc._lib.lib().msda_last_launch_path() == dvc._lib.PATH_MATCH
+    for l in range(layers):
+        want = m.cost_matrix(logits[l][None], boxes[l][None], labels, tboxes)
+        scale = float(want.abs().max())
+        err = float((cost[l] - want).abs().max())
+        assert err <= 2 * np.finfo(np.float32).eps * scale, (l, err, scale)
+        a, c = linear_sum_assignment(want.cpu().numpy())
+        assert q_idx[l].tolist() == a.tolist() and t_idx[l].tolist() == c.tolist()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("graphs", [False, True])
 def test_step_with_device_matching_reproduces_host_matching(graphs):
     """The two-stage PDVC step, device matching against host (scipy) matching: same assignment, same losses, same gradients."""
