@@ -272,9 +272,9 @@ class LossStage(nn.Module):
                 s_.wait_stream(main)
             with (torch.cuda.stream(side[0]) if side else contextlib.nullcontext()):
                 layer = torch.arange(n_pred, device=hs.device)[:, None]
-                hs_pairs = hs[:, 0][layer, q_idx].reshape(1, n_pred * pairs, -1)
+                hs_pairs = hs.squeeze(1)[layer, q_idx].reshape(1, n_pred * pairs, -1)       # squeeze: a view, no select in backward
                 valid = valid_ratios[0]                                                     # (L,)
-                first = init_reference[0, q_idx[0]] * valid[None, :]                        # (pairs, L)
+                first = init_reference.squeeze(0)[q_idx[0]] * valid[None, :]                        # (pairs, L)
                 width = (2.0 * head.core.n_points) / shapes.to(first.dtype)
                 refs = [torch.stack([first, width[None, :].expand_as(first)], -1)]
                 if n_pred > 1:
@@ -291,8 +291,9 @@ class LossStage(nn.Module):
             cap, side, main = self._caption_losses_per_layer(hs, init_reference, inter_references, others, cap_tensor,
                                                              cap_mask, q_idx, t_idx)
         set_losses = []
+        logits_l, counts_l, boxes_l = logits.unbind(0), counts.unbind(0), boxes.unbind(0)   # one stack each in backward
         for lid in range(n_pred):
-            out = {'pred_logits': logits[lid], 'pred_count': counts[lid], 'pred_boxes': boxes[lid]}
+            out = {'pred_logits': logits_l[lid], 'pred_count': counts_l[lid], 'pred_boxes': boxes_l[lid]}
             set_losses.append(crit.layer_losses(out, targets, (batch, q_idx[lid], [t_idx[lid]]), [pairs], num_boxes))
         for s_ in side:
             main.wait_stream(s_)

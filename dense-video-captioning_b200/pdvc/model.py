@@ -184,7 +184,10 @@ class ShowAttendTellCore(nn.Module):
         the recurrence (same weights; SentenceDecoder makes them per decoding run)."""
         n, lq = reference_points.shape[:2]
         k = self.n_levels * self.n_points
-        joint_query = torch.cat((state[0][-1].unsqueeze(0), query), 2)
+        # the top layer's hidden state, taken ONCE: every `state[0][-1]` is a select whose backward is a zero-fill + copy +
+        # accumulation on the recurrence's critical path; StepLSTM hands the state over as 2-D tensors (no select at all)
+        h_prev = state[0] if state[0].dim() == 2 else state[0][-1]
+        joint_query = torch.cat((h_prev.unsqueeze(0), query), 2)
         extra = {}
         if step_linears is not None:
             extra["sampling_offsets"] = step_linears["sampling_offsets"](joint_query)
@@ -198,7 +201,7 @@ class ShowAttendTellCore(nn.Module):
             # border mode, so sampling the projected rows IS ctx2att of the sampled rows (LSTM_DSA.py:247) without the
             # per-word GEMM, its two backward GEMMs and the per-word weight-gradient accumulation
             if USE_FUSED_ATTEND and CaptionAttendFunction.supported(clip, k, self.att_feat_size):
-                attended = CaptionAttendFunction.apply(clip.reshape(n * lq * self.n_heads, k, -1), h2att(state[0][-1]),
+                attended = CaptionAttendFunction.apply(clip.reshape(n * lq * self.n_heads, k, -1), h2att(h_prev),
                                                        self.alpha_net.weight, self.alpha_net.bias, self.att_feat_size)
                 clip = None
             else:
@@ -206,13 +209,15 @@ class ShowAttendTellCore(nn.Module):
         else:
             ctx = self.ctx2att(clip)
         if clip is not None:
-            scores = ctx + h2att(state[0][-1])[:, None, None, :]
+            scores = ctx + h2att(h_prev)[:, None, None, :]
             scores = self.alpha_net(torch.tanh(scores)).view(-1, k)
             weight = F.softmax(scores, dim=1)
             attended = torch.bmm(weight.unsqueeze(1), clip.reshape(-1, k, self.att_feat_size)).squeeze(1)
         attended = attended.reshape(n * lq, self.n_heads * self.att_feat_size)
         if step_linears is not None and "lstm" in step_linears:
             return step_linears["lstm"](attended, state)
+        if state[0].dim() == 2:
+            state = (state[0].unsqueeze(0), state[1].unsqueeze(0))
         step_in = torch.cat((xt.unsqueeze(0), attended.unsqueeze(0), query), 2)
         out, state = self.rnn(step_in, state)
         return out.squeeze(0), state
@@ -240,11 +245,12 @@ class StepLSTM:
         return rnn.num_layers == 1 and not rnn.bias and not rnn.bidirectional and rnn.weight_ih_l0.dtype == torch.float32
 
     def __call__(self, attended, state):
-        h_prev, c_prev = state[0][-1], state[1][-1]
+        """state: (h, c) as (pairs, H) tensors -- or nn.LSTM's (1, pairs, H) on the first step; returned 2-D."""
+        h_prev, c_prev = (state[0], state[1]) if state[0].dim() == 2 else (state[0][-1], state[1][-1])
         rec = self.rec(torch.cat((attended.float(), h_prev.float()), 1))
         h, c = LSTMCellFunction.apply(self.pre[self.i], rec, c_prev)
         self.i += 1
-        return h, (h.unsqueeze(0), c.unsqueeze(0))
+        return h, (h, c)
 
 
 class LSTMDSACaptioner(nn.Module):
@@ -416,9 +422,11 @@ class PDVC(nn.Module):
     def forward_heads(self, hs, init_reference, inter_references):
         """Class / count / segment heads on every decoder layer (pdvc.py:246-266) -> stacked (Ld, N, ...) tensors."""
         logits, counts, boxes = [], [], []
+        # unbind, not hs[lid]: one stack in backward instead of a zero-fill + copy + accumulation per layer
+        layers, refs = hs.unbind(0), (inter_references.unbind(0) if hs.shape[0] > 1 else ())
         for lid in range(hs.shape[0]):
-            state = hs[lid]
-            reference = init_reference if lid == 0 else inter_references[lid - 1]
+            state = layers[lid]
+            reference = init_reference if lid == 0 else refs[lid - 1]
             delta = self.bbox_head[lid](state)
             unact = inverse_sigmoid(reference)
             if reference.shape[-1] == 2:
