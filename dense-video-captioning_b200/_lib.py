@@ -16,7 +16,7 @@ CSRC = os.path.join(_HERE, "csrc")
 
 F32, BF16, F64 = 0, 1, 2
 PAD_BORDER, PAD_ZEROS = 0, 1
-FLAG_ASSUME_1D, FLAG_FORCE_GENERIC, FLAG_NO_SMALL = 1, 2, 4
+FLAG_ASSUME_1D, FLAG_FORCE_GENERIC, FLAG_NO_SMALL, FLAG_ACCUMULATE = 1, 2, 4, 8
 STATIC_SCRATCH_BYTES = 16 << 20    # MSDA_STATIC_SCRATCH_BYTES
 ERR_STATIC_SCRATCH = -8
 PATH_NONE, PATH_LEAN, PATH_TILE, PATH_FAST, PATH_GENERIC, PATH_SMALL, PATH_PROJ, PATH_MATCH = range(8)

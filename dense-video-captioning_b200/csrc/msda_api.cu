@@ -911,7 +911,6 @@ int msda_cap_sample_backward(const void *value, const int64_t *temporal_shapes, 
                              void *workspace, size_t workspace_bytes, int N, int S, int M, int D, int L, int Lq, int P,
                              int R, int dtype, int pad_mode, unsigned flags, void *stream)
 {
-    (void)flags;
     g_launches = 0; g_path = MSDA_PATH_NONE;
     const Dims d{N, S, M, D, L, Lq, P};
     if (int e = check_dims(d, dtype, pad_mode)) return e;
@@ -919,6 +918,10 @@ int msda_cap_sample_backward(const void *value, const int64_t *temporal_shapes, 
     if (!value || !temporal_shapes || !level_start_index || !reference_points || !sampling_offsets || !grad_samples ||
         !grad_value || !grad_sampling_offsets)
         return MSDA_ERR_NULL;
+    // MSDA_FLAG_ACCUMULATE: grad_value / grad_reference_points already hold the sum of earlier calls (the word steps of one
+    // decoding run sample the same value tensor around the same reference points): add to them instead of zero-filling
+    const bool accumulate = (flags & MSDA_FLAG_ACCUMULATE) != 0;
+    if (accumulate && dtype != MSDA_F32) return MSDA_ERR_UNSUPPORTED;
     if (!aligned16(value) || !aligned16(grad_samples) || !aligned16(grad_value)) return MSDA_ERR_ALIGN;
     const int ch = dtype == MSDA_BF16 ? 8 : 4;
     if (dtype == MSDA_F64 || D % ch) return MSDA_ERR_UNSUPPORTED;
@@ -928,9 +931,10 @@ int msda_cap_sample_backward(const void *value, const int64_t *temporal_shapes, 
     const long long nv = (long long)N * S * M * D;
     const long long ns = (long long)N * Lq * M * L * P;
     void *acc = dtype == MSDA_BF16 ? workspace : grad_value;
-    if (int e = memset_async(acc, (size_t)nv * 4, st)) return e;
+    if (!accumulate)
+        if (int e = memset_async(acc, (size_t)nv * 4, st)) return e;
     if (int e = memset_async(grad_sampling_offsets, (size_t)ns * 4, st)) return e;
-    if (grad_reference_points)
+    if (grad_reference_points && !accumulate)
         if (int e = memset_async(grad_reference_points, (size_t)N * Lq * L * R * 4, st)) return e;
     CapArgs a{};
     a.value = value; a.shapes = temporal_shapes; a.lsi = level_start_index; a.ref = reference_points;

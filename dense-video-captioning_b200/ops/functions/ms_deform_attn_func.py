@@ -362,7 +362,10 @@ class MSDeformCapSampleFunction(Function):
         return value.dtype in (torch.float32, torch.bfloat16) and value.shape[-1] % ch == 0
 
     @staticmethod
-    def forward(ctx, value, temporal_shapes, level_start_index, reference_points, sampling_offsets, padding_mode=None):
+    def forward(ctx, value, temporal_shapes, level_start_index, reference_points, sampling_offsets, padding_mode=None,
+                run=None):
+        """run: a StepSampleRun when this call is one word step of a decoding run (same value / reference points at
+        every step): the steps' backward passes then add their grad_value / grad_reference_points into ONE buffer."""
         _check_cuda_contig(value=value, temporal_shapes=temporal_shapes, level_start_index=level_start_index,
                            reference_points=reference_points, sampling_offsets=sampling_offsets)
         _require(value.dtype in (torch.float32, torch.bfloat16), "fused sampler takes float32 or bfloat16 values")
@@ -387,6 +390,9 @@ class MSDeformCapSampleFunction(Function):
                 _stream(value.device))
         _lib.check(rc, "msda_cap_sample_forward")
         ctx.pad = pad
+        ctx.run, ctx.index = None, 0
+        if run is not None and value.dtype == torch.float32:
+            ctx.run, ctx.index = run, run.enter(value, reference_points)
         ctx.save_for_backward(value, temporal_shapes, level_start_index, reference_points, sampling_offsets)
         return out
 
@@ -399,9 +405,16 @@ class MSDeformCapSampleFunction(Function):
         R = ref.shape[-1]
         grad_samples = grad_samples.contiguous()
         _require(grad_samples.dtype == value.dtype, "grad_samples dtype must match value")
-        grad_value = torch.empty_like(value)
+        run, flags = ctx.run, 0
+        if run is not None:
+            # one zero-filled buffer per decoding run; every step's kernel adds into it (MSDA_FLAG_ACCUMULATE) and step 0,
+            # whose backward runs last, hands it to autograd -- instead of a zero-fill and an accumulation per step
+            grad_value, grad_ref = run.buffers(value, ref, ctx.needs_input_grad[3])
+            flags = _lib.FLAG_ACCUMULATE
+        else:
+            grad_value = torch.empty_like(value)
+            grad_ref = torch.empty_like(ref) if ctx.needs_input_grad[3] else None
         grad_off = torch.empty_like(off)
-        grad_ref = torch.empty_like(ref) if ctx.needs_input_grad[3] else None
         lib = _lib.lib()
         code = _DTYPES[value.dtype]
         ws_bytes = lib.msda_backward_workspace_bytes(N, S, M, D, code)
@@ -409,10 +422,50 @@ class MSDeformCapSampleFunction(Function):
         with torch.cuda.device(value.device):
             rc = lib.msda_cap_sample_backward(
                 _ptr(value), _ptr(shapes), _ptr(lsi), _ptr(ref), _ptr(off), _ptr(grad_samples), _ptr(grad_value),
-                _ptr(grad_ref), _ptr(grad_off), _ptr(ws), ws_bytes, N, S, M, D, L, Lq, P, R, code, ctx.pad, 0,
+                _ptr(grad_ref), _ptr(grad_off), _ptr(ws), ws_bytes, N, S, M, D, L, Lq, P, R, code, ctx.pad, flags,
                 _stream(value.device))
         _lib.check(rc, "msda_cap_sample_backward")
-        return grad_value, None, None, grad_ref, grad_off, None
+        if run is not None and not run.leave(ctx.index):
+            return None, None, None, None, grad_off, None, None        # the sums travel with step 0
+        return grad_value, None, None, grad_ref, grad_off, None, None
+
+
+class StepSampleRun:
+    """The word steps of ONE teacher-forced decoding run through MSDeformCapSampleFunction (LSTM_DSA.py:74-96 calls the
+    sampler once per word on the same memory and reference points): their gradients with respect to the value tensor and
+    the reference points are sums over the steps, formed here in one buffer by the kernels themselves.  Steps are entered
+    in order 0, 1, 2, ...; their backward passes run last-to-first (every step depends on the previous one through the
+    LSTM state), which `leave` checks."""
+
+    def __init__(self):
+        self.calls = 0
+        self._value = self._ref = None
+        self._grad_value = self._grad_ref = None
+        self._left = None
+
+    def enter(self, value, ref):
+        if self.calls == 0:
+            self._value, self._ref = value, ref
+        _require(value is self._value or value.data_ptr() == self._value.data_ptr(), "StepSampleRun: one value tensor per run")
+        _require(ref is self._ref or ref.data_ptr() == self._ref.data_ptr(), "StepSampleRun: one reference tensor per run")
+        index, self.calls = self.calls, self.calls + 1
+        return index
+
+    def buffers(self, value, ref, need_ref):
+        if self._left is None:
+            self._left = self.calls
+            self._grad_value = torch.zeros_like(value)
+            self._grad_ref = torch.zeros_like(ref) if need_ref else None
+        return self._grad_value, self._grad_ref
+
+    def leave(self, index):
+        """True for the step that hands the sums to autograd (step 0, the last one to run)."""
+        self._left -= 1
+        _require(index == self._left, "StepSampleRun: backward passes must run from the last step to the first, each once")
+        if index != 0:
+            return False
+        self.calls, self._left, self._value, self._ref = 0, None, None, None
+        return True
 
 
 class ProjLinearFunction(Function):

@@ -23,7 +23,7 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
-from ..ops.functions import CaptionAttendFunction, LSTMCellFunction, StepLinear, get_default_padding_mode
+from ..ops.functions import CaptionAttendFunction, LSTMCellFunction, StepLinear, StepSampleRun, get_default_padding_mode
 from ..ops.modules import MSDeformAttnCap
 from .transformer import DeformableTransformer, inverse_sigmoid
 
@@ -31,6 +31,7 @@ from .transformer import DeformableTransformer, inverse_sigmoid
 USE_FP32_SAMPLES = True    # bf16 autocast: caption-head samples (two projected-memory rows per sample) kept in fp32
 USE_FUSED_ATTEND = True    # one kernel each way for the soft attention over the samples (csrc/msda_capattend.cuh)
 USE_STEP_LSTM = True       # hoisted input projections + fused cell kernel instead of cuDNN's single-step LSTM
+USE_STEP_SAMPLE_RUN = True # the word steps' sampler backward passes add into one grad_value / grad_reference buffer
 USE_STEP_LINEAR = True     # few-row kernels + deferred weight gradients for the Linear layers on the caption recurrence
 
 
@@ -191,9 +192,17 @@ class ShowAttendTellCore(nn.Module):
         extra = {}
         if step_linears is not None:
             extra["sampling_offsets"] = step_linears["sampling_offsets"](joint_query)
-        clip = self.deformable_att(joint_query, reference_points, memory, temporal_shapes, level_start_index,
-                                   padding_mask, projected_value=projected_value, **extra)   # (N*M, D', Lq, L, P)
-        clip = clip.reshape(n, self.n_heads, -1, lq, k).permute(0, 3, 1, 4, 2)            # (N, Lq, M, L*P, D')
+            if "sample_run" in step_linears and getattr(self.deformable_att, "supports_rows_layout", False):
+                extra["sample_run"] = step_linears["sample_run"]
+        # the reference takes (N*M, D', Lq, L, P) and permutes it to (N, Lq, M, L*P, D') (LSTM_DSA.py:239-243); the CUDA
+        # module hands the samples over in that layout directly (no transposing copies)
+        if getattr(self.deformable_att, "supports_rows_layout", False):
+            clip = self.deformable_att(joint_query, reference_points, memory, temporal_shapes, level_start_index,
+                                       padding_mask, projected_value=projected_value, rows_layout=True, **extra)
+        else:
+            clip = self.deformable_att(joint_query, reference_points, memory, temporal_shapes, level_start_index,
+                                       padding_mask, projected_value=projected_value, **extra)   # (N*M, D', Lq, L, P)
+            clip = clip.reshape(n, self.n_heads, -1, lq, k).permute(0, 3, 1, 4, 2)        # (N, Lq, M, L*P, D')
         clip = clip.reshape(n * lq, self.n_heads, k, -1)
         h2att = step_linears["h2att"] if step_linears is not None else self.h2att
         if clip.shape[-1] == self.att_feat_size + self.att_hid_size:
@@ -340,6 +349,8 @@ class SentenceDecoder:
                                  "sampling_offsets": StepLinear(core.deformable_att.sampling_offsets)}
             if USE_STEP_LSTM and StepLSTM.supported(core.rnn):
                 self.step_linears["lstm"] = StepLSTM(core.rnn, self.embedded, hs)
+            if USE_STEP_SAMPLE_RUN and self.value.dtype == torch.float32:
+                self.step_linears["sample_run"] = StepSampleRun()
         self.outputs = []
 
     def step(self, i):

@@ -57,6 +57,8 @@ enum { MSDA_PAD_BORDER = 0, MSDA_PAD_ZEROS = 1 };
                                     reference computes for y = 0.5: exactly 0 under BORDER, and
                                     -attn * grad_attn under ZEROS (ms_deform_im2col_cuda.cuh:159) */
 #define MSDA_FLAG_FORCE_GENERIC 2u /* testing: take the generic (any-D, 2-D capable) kernels */
+#define MSDA_FLAG_ACCUMULATE 8u    /* msda_cap_sample_backward, f32: add into grad_value / grad_reference_points instead of
+                                      overwriting them (the caller zero-fills once per decoding run; csrc/msda_api.cu) */
 #define MSDA_FLAG_NO_SMALL 4u      /* testing: never take the single-phase kernels for small problems
                                       (csrc/msda_small.cuh), so that the staged kernels can be checked on small inputs */
 

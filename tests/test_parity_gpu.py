@@ -610,13 +610,14 @@ def test_step_lstm_matches_nn_lstm_float64():
         step = stepper(module, emb, q)
         outs = []
         for i in range(steps):
-            a = att[i] + state[0][-1] @ m
+            h_prev = state[0] if state[0].dim() == 2 else state[0][-1]     # StepLSTM hands its state on as (B, H) tensors
+            a = att[i] + h_prev @ m
             out, state = step(i, emb, q, a, state)
             outs.append(out)
         outs = torch.stack(outs)
         loss = (outs ** 2).sum() + (state[1] ** 2).sum()
         grads = torch.autograd.grad(loss, [emb, q, att, module.weight_ih_l0, module.weight_hh_l0])
-        return [outs.detach(), state[1].detach()] + [g for g in grads]
+        return [outs.detach(), state[1].detach().reshape(1, B, H)] + [g for g in grads]
 
     def ref_stepper(module, emb, q):
         def step(i, emb, q, a, state):
@@ -663,3 +664,31 @@ def test_caption_attend_matches_torch_float64(B, M, K, D, A):
         scale = max(float(b.abs().max()), 1.0 if name == "grad_alpha_bias" else 0.0)
         assert a.shape == b.shape, name
         assert float((a.double().cpu() - b).abs().max()) <= 2e-5 * scale, name
+
+
+def test_sample_run_accumulates_like_autograd():
+    """MSDA_FLAG_ACCUMULATE / StepSampleRun: three sampler calls on one value tensor and one set of reference points, their
+    backward passes adding into one buffer, against the same three calls with autograd's own accumulation (2e-6 of max|g|:
+    the two differ only in the order of fp32 additions)."""
+    from dense_video_captioning_b200.ops.functions import MSDeformCapSampleFunction, StepSampleRun
+    g = torch.Generator().manual_seed(11)
+    N, S, M, D, Lq, P = 1, 375, 1, 64, 7, 4
+    T = torch.tensor([200, 100, 50, 25], device="cuda")
+    lsi = torch.cat((T.new_zeros(1), T.cumsum(0)[:-1]))
+    res = {}
+    for use_run in (False, True):
+        value = torch.randn(N, S, M, D, generator=g.manual_seed(11)).cuda().requires_grad_(True)
+        ref = torch.stack([torch.rand(N, Lq, 4, generator=g), torch.rand(N, Lq, 4, generator=g) * 0.3 + 0.05], -1).cuda().requires_grad_(True)
+        run = StepSampleRun() if use_run else None
+        total, offs = 0, []
+        for step in range(3):
+            off = (torch.randn(N, Lq, M, 4, P, generator=g) * 2).cuda().requires_grad_(True)
+            offs.append(off)
+            out = MSDeformCapSampleFunction.apply(value, T, lsi, ref, off, "border", run)
+            total = total + (out * (step + 1)).sum() + total * 0.5     # later steps depend on earlier ones, as in the word loop
+        total.backward()
+        res[use_run] = [value.grad, ref.grad] + [o.grad for o in offs]
+        if use_run:
+            assert run.calls == 0 and run._left is None               # the run closed itself
+    for a, b in zip(res[False], res[True]):
+        assert float((a - b).abs().max()) <= 2e-6 * float(a.abs().max())

@@ -19,7 +19,7 @@ def main():
     for _ in range(3):
         tr.step(video)
     torch.cuda.synchronize()
-    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=True) as prof:
         tr.step(video)
         torch.cuda.synchronize()
     rows = []
@@ -29,6 +29,17 @@ def main():
     print(f"{'calls':>6}  {'self device us':>14}  name")
     for count, key, dev in rows[:90]:
         print(f"{count:6d}  {dev:14.1f}  {key[:110]}")
+
+
+    print("\nby input shape (elementwise / reduction ops with >= 4 calls):")
+    rows = []
+    for e in prof.key_averages(group_by_input_shape=True):
+        if e.key in ("aten::add_", "aten::add", "aten::mul", "aten::copy_", "aten::cat", "aten::sum", "aten::div", "aten::fill_",
+                     "aten::sub", "aten::neg", "aten::mm", "aten::addmm", "aten::clamp", "aten::index", "aten::stack") and e.count >= 4:
+            rows.append((e.count, e.key, str(e.input_shapes)[:110]))
+    rows.sort(key=lambda r: -r[0])
+    for count, key, shapes in rows[:70]:
+        print(f"{count:6d}  {key:14s} {shapes}")
 
 
 if __name__ == "__main__":
