@@ -697,8 +697,11 @@ class CaptionAttendFunction(Function):
 
     @staticmethod
     @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
-    def forward(ctx, samples, hproj, alpha_weight, alpha_bias, D):
+    def forward(ctx, samples, hproj, alpha_weight, alpha_bias, D, run=None):
+        """run: a StepAttendRun when this call is one word step of a decoding run: the steps' alpha_net gradients are then
+        reduced once for the whole run instead of once per word (plus two accumulations per word in autograd)."""
         samples, hproj = samples.contiguous(), hproj.contiguous()
+        ctx.run, ctx.index = run, (run.enter() if run is not None else 0)
         ctx.alpha_shape = alpha_weight.shape
         alpha_weight, alpha_bias = alpha_weight.contiguous().view(-1), alpha_bias.contiguous().view(-1)
         _check_cuda_contig(samples=samples, hproj=hproj, alpha_weight=alpha_weight, alpha_bias=alpha_bias)
@@ -726,7 +729,11 @@ class CaptionAttendFunction(Function):
         grad_attended = grad_attended.contiguous().float()
         grad_samples = torch.empty_like(samples)
         grad_hproj = torch.empty((BM, A), dtype=torch.float32, device=samples.device)
-        grad_alpha = torch.empty((BM, A + 1), dtype=torch.float32, device=samples.device)
+        run = ctx.run
+        if run is not None:
+            grad_alpha = run.rows(ctx.index, BM, A + 1, samples.device)     # this step's slot of the run's (steps, BM, A+1)
+        else:
+            grad_alpha = torch.empty((BM, A + 1), dtype=torch.float32, device=samples.device)
         with torch.cuda.device(samples.device):
             rc = _lib.lib().msda_cap_attend_backward_f32(_ptr(samples), _ptr(hproj), _ptr(alpha_weight), _ptr(weight),
                                                          _ptr(grad_attended), _ptr(grad_samples), _ptr(grad_hproj),
@@ -734,5 +741,39 @@ class CaptionAttendFunction(Function):
         _lib.check(rc, "msda_cap_attend_backward_f32")
         if M > 1:
             grad_hproj = grad_hproj.view(BM // M, M, A).sum(1)
-        total = grad_alpha.sum(0)
-        return grad_samples, grad_hproj, total[:A].view(ctx.alpha_shape), total[A:], None
+        if run is not None:
+            total = run.leave(ctx.index)
+            if total is None:
+                return grad_samples, grad_hproj, None, None, None, None     # alpha_net's gradients travel with step 0
+        else:
+            total = grad_alpha.sum(0)
+        return grad_samples, grad_hproj, total[:A].view(ctx.alpha_shape), total[A:], None, None
+
+
+class StepAttendRun:
+    """The word steps of ONE decoding run through CaptionAttendFunction: every step's backward writes its per-row alpha_net
+    gradients into its slot of one (steps, BM, A+1) buffer; step 0 -- whose backward runs last -- reduces the buffer once."""
+
+    def __init__(self):
+        self.calls = 0
+        self._buf = None
+        self._left = None
+
+    def enter(self):
+        index, self.calls = self.calls, self.calls + 1
+        return index
+
+    def rows(self, index, bm, width, device):
+        if self._left is None:
+            self._left = self.calls
+            self._buf = torch.empty((self.calls, bm, width), dtype=torch.float32, device=device)
+        return self._buf[index]
+
+    def leave(self, index):
+        self._left -= 1
+        _require(index == self._left, "StepAttendRun: backward passes must run from the last step to the first, each once")
+        if index != 0:
+            return None
+        total = self._buf.view(-1, self._buf.shape[-1]).sum(0)
+        self.calls, self._left, self._buf = 0, None, None
+        return total

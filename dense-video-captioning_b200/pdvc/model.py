@@ -23,7 +23,7 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
-from ..ops.functions import CaptionAttendFunction, LSTMCellFunction, StepLinear, StepSampleRun, get_default_padding_mode
+from ..ops.functions import CaptionAttendFunction, LSTMCellFunction, StepAttendRun, StepLinear, StepSampleRun, get_default_padding_mode
 from ..ops.modules import MSDeformAttnCap
 from .transformer import DeformableTransformer, inverse_sigmoid
 
@@ -211,7 +211,8 @@ class ShowAttendTellCore(nn.Module):
             # per-word GEMM, its two backward GEMMs and the per-word weight-gradient accumulation
             if USE_FUSED_ATTEND and CaptionAttendFunction.supported(clip, k, self.att_feat_size):
                 attended = CaptionAttendFunction.apply(clip.reshape(n * lq * self.n_heads, k, -1), h2att(h_prev),
-                                                       self.alpha_net.weight, self.alpha_net.bias, self.att_feat_size)
+                                                       self.alpha_net.weight, self.alpha_net.bias, self.att_feat_size,
+                                                       step_linears.get("attend_run") if step_linears else None)
                 clip = None
             else:
                 clip, ctx = clip[..., :self.att_feat_size], clip[..., self.att_feat_size:]
@@ -351,6 +352,7 @@ class SentenceDecoder:
                 self.step_linears["lstm"] = StepLSTM(core.rnn, self.embedded, hs)
             if USE_STEP_SAMPLE_RUN and self.value.dtype == torch.float32:
                 self.step_linears["sample_run"] = StepSampleRun()
+                self.step_linears["attend_run"] = StepAttendRun()
         self.outputs = []
 
     def step(self, i):
