@@ -13,6 +13,7 @@ of the caption tensor, one cost-matrix transfer for all decoder layers) and the 
 memory once per sentence instead of once per word.
 """
 import copy
+import contextlib
 import math
 
 from dataclasses import dataclass, field
@@ -31,6 +32,7 @@ from .transformer import DeformableTransformer, inverse_sigmoid
 USE_FP32_SAMPLES = True    # bf16 autocast: caption-head samples (two projected-memory rows per sample) kept in fp32
 USE_FUSED_ATTEND = True    # one kernel each way for the soft attention over the samples (csrc/msda_capattend.cuh)
 USE_STEP_LSTM = True       # hoisted input projections + fused cell kernel instead of cuDNN's single-step LSTM
+PARALLEL_POSITION_EMBEDDING = True   # masks + position embeddings of the pyramid on a side stream beside the projections
 USE_STEP_SAMPLE_RUN = True # the word steps' sampler backward passes add into one grad_value / grad_reference buffer
 USE_STEP_LINEAR = True     # few-row kernels + deferred weight gradients for the Linear layers on the caption recurrence
 
@@ -96,17 +98,30 @@ class PositionEmbeddingSine(nn.Module):
         self.max_duration = 256
         self.duration_embed_layer = nn.Linear(self.max_duration, self.max_duration)
 
-    def forward(self, mask, duration):
-        """mask (N,T) True = padding; duration (N,) seconds -> (N, 2*num_pos_feats, T)."""
+    def duration_embedding(self, duration, device):
+        """(N, max_duration): first int(duration) units on, the rest off (position_encoding.py:60-66) without a host loop.
+        The same vector for every pyramid level of a video: BaseEncoder forms it once per forward."""
+        units = torch.arange(self.max_duration, device=device)[None] < duration.int()[:, None]
+        return self.duration_embed_layer(units.to(self.duration_embed_layer.weight.dtype))
+
+    def frequencies(self, device):
+        """temperature ** (2 * (i // 2) / num_pos_feats), i < num_pos_feats: constants, formed once per device."""
+        key = str(device)
+        if key not in self.__dict__.setdefault("_dim_t", {}):
+            dim_t = torch.arange(self.num_pos_feats, dtype=torch.float32, device=device)
+            self._dim_t[key] = self.temperature ** (2 * (dim_t // 2) / self.num_pos_feats)
+        return self._dim_t[key]
+
+    def forward(self, mask, duration, dur=None):
+        """mask (N,T) True = padding; duration (N,) seconds -> (N, 2*num_pos_feats, T).  `dur`: duration_embedding(duration)
+        when the caller has it already."""
         steps = (~mask).cumsum(1, dtype=torch.float32)
         steps = (steps - 0.5) / (steps[:, -1:] + 1e-6) * self.scale
-        dim_t = torch.arange(self.num_pos_feats, dtype=torch.float32, device=mask.device)
-        dim_t = self.temperature ** (2 * (dim_t // 2) / self.num_pos_feats)
-        ang = steps[:, :, None] / dim_t
+        ang = steps[:, :, None] / self.frequencies(mask.device)
         pos_x = torch.stack((ang[:, :, 0::2].sin(), ang[:, :, 1::2].cos()), dim=3).flatten(2)
-        # first int(duration) units on, the rest off (position_encoding.py:60-66) without a host loop
-        units = torch.arange(self.max_duration, device=mask.device)[None] < duration.int()[:, None]
-        dur = self.duration_embed_layer(units.to(self.duration_embed_layer.weight.dtype))[:, None, :].expand(-1, pos_x.shape[1], -1)
+        if dur is None:
+            dur = self.duration_embedding(duration, mask.device)
+        dur = dur[:, None, :].expand(-1, pos_x.shape[1], -1)
         return torch.cat((pos_x, dur), dim=2).permute(0, 2, 1)
 
 
@@ -134,13 +149,31 @@ class BaseEncoder(nn.Module):
 
     def forward(self, vf, mask, duration):
         x = vf.transpose(1, 2)
-        srcs, masks, poses = [self.input_proj[0](x)], [mask], [self.pos_embed(mask, duration)]
+        # level lengths of the stride-2 convolutions (k3, s2, p1): known without running them, so the masks and position
+        # embeddings of all levels -- which depend on the mask and the duration only -- are formed on a side stream while
+        # the projection chain runs (a parallel branch of the captured graph, forward and backward)
+        lengths = [x.shape[-1]]
+        for _ in range(1, self.num_feature_levels):
+            lengths.append((lengths[-1] - 1) // 2 + 1)
+        side = main = None
+        if x.is_cuda and PARALLEL_POSITION_EMBEDDING:
+            main = torch.cuda.current_stream(x.device)
+            side = self.__dict__.setdefault("_side_stream", {}).setdefault(str(x.device), torch.cuda.Stream(x.device))
+            side.wait_stream(main)
+        with (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):
+            dur = self.pos_embed.duration_embedding(duration, mask.device)
+            masks = [mask] + [F.interpolate(mask[None].float(), size=(t,)).to(torch.bool)[0] for t in lengths[1:]]
+            poses = [self.pos_embed(m, duration, dur) for m in masks]
+        srcs = [self.input_proj[0](x)]
         for lvl in range(1, self.num_feature_levels):
-            src = self.input_proj[lvl](x if lvl == 1 else srcs[-1])
-            m = F.interpolate(mask[None].float(), size=src.shape[-1:]).to(torch.bool)[0]
-            srcs.append(src)
-            masks.append(m)
-            poses.append(self.pos_embed(m, duration).to(src.dtype))
+            srcs.append(self.input_proj[lvl](x if lvl == 1 else srcs[-1]))
+            assert srcs[-1].shape[-1] == lengths[lvl]
+        if side is not None:
+            main.wait_stream(side)
+            if not torch.cuda.is_current_stream_capturing():      # eager: the allocator must know the main stream reads them
+                for t in poses + masks:
+                    t.record_stream(main)
+        poses = [p.to(src.dtype) for p, src in zip(poses, srcs)]
         return srcs, masks, poses
 
 
