@@ -32,6 +32,7 @@ from .transformer import DeformableTransformer, inverse_sigmoid
 USE_FP32_SAMPLES = True    # bf16 autocast: caption-head samples (two projected-memory rows per sample) kept in fp32
 USE_FUSED_ATTEND = True    # one kernel each way for the soft attention over the samples (csrc/msda_capattend.cuh)
 USE_STEP_LSTM = True       # hoisted input projections + fused cell kernel instead of cuDNN's single-step LSTM
+PARALLEL_HEADS = True                # class / count / segment heads of the decoder layers on one stream per layer
 PARALLEL_POSITION_EMBEDDING = True   # masks + position embeddings of the pyramid on a side stream beside the projections
 USE_STEP_SAMPLE_RUN = True # the word steps' sampler backward passes add into one grad_value / grad_reference buffer
 USE_STEP_LINEAR = True     # few-row kernels + deferred weight gradients for the Linear layers on the caption recurrence
@@ -467,21 +468,38 @@ class PDVC(nn.Module):
 
     def forward_heads(self, hs, init_reference, inter_references):
         """Class / count / segment heads on every decoder layer (pdvc.py:246-266) -> stacked (Ld, N, ...) tensors."""
-        logits, counts, boxes = [], [], []
+        n_layers = hs.shape[0]
+        logits, counts, boxes = [None] * n_layers, [None] * n_layers, [None] * n_layers
         # unbind, not hs[lid]: one stack in backward instead of a zero-fill + copy + accumulation per layer
-        layers, refs = hs.unbind(0), (inter_references.unbind(0) if hs.shape[0] > 1 else ())
-        for lid in range(hs.shape[0]):
-            state = layers[lid]
-            reference = init_reference if lid == 0 else refs[lid - 1]
-            delta = self.bbox_head[lid](state)
-            unact = inverse_sigmoid(reference)
-            if reference.shape[-1] == 2:
-                delta = delta + unact
-            else:
-                delta = torch.cat((delta[..., :1] + unact, delta[..., 1:]), -1)
-            logits.append(self.class_head[lid](state))
-            counts.append(self.count_head[lid](state.max(dim=1)[0]))
-            boxes.append(delta.sigmoid())
+        layers, refs = hs.unbind(0), (inter_references.unbind(0) if n_layers > 1 else ())
+        # the layers' heads are independent of each other: one stream per layer (parallel branches of the captured graph)
+        side, main = [], None
+        if hs.is_cuda and PARALLEL_HEADS and n_layers > 1:
+            main = torch.cuda.current_stream(hs.device)
+            pool = self.__dict__.setdefault("_head_streams", {}).setdefault(str(hs.device), [])
+            while len(pool) < n_layers - 1:
+                pool.append(torch.cuda.Stream(hs.device))
+            side = pool[:n_layers - 1]
+            for s_ in side:
+                s_.wait_stream(main)
+        for lid in range(n_layers):
+            with (torch.cuda.stream(side[lid - 1]) if (side and lid > 0) else contextlib.nullcontext()):
+                state = layers[lid]
+                reference = init_reference if lid == 0 else refs[lid - 1]
+                delta = self.bbox_head[lid](state)
+                unact = inverse_sigmoid(reference)
+                if reference.shape[-1] == 2:
+                    delta = delta + unact
+                else:
+                    delta = torch.cat((delta[..., :1] + unact, delta[..., 1:]), -1)
+                logits[lid] = self.class_head[lid](state)
+                counts[lid] = self.count_head[lid](state.max(dim=1)[0])
+                boxes[lid] = delta.sigmoid()
+        for s_ in side:
+            main.wait_stream(s_)
+        if side and not torch.cuda.is_current_stream_capturing():
+            for t in logits[1:] + counts[1:] + boxes[1:]:
+                t.record_stream(main)
         return torch.stack(logits), torch.stack(counts), torch.stack(boxes)
 
     def forward(self, dt, criterion):
