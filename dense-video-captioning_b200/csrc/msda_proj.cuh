@@ -22,13 +22,19 @@
 // cost what three TF32 products would.
 //
 // Structure of one CTA (256 threads, one 128 x BN output tile, one slice of the reduction axis):
-//   all threads   global -> registers (16-byte loads, next block prefetched) -> [bf16 x 3 split] -> shared memory in the
-//                 canonical no-swizzle UMMA layout (8 x 16-byte core matrices), two stages
-//   thread 0      fence.proxy.async + tcgen05.mma for the staged block, tcgen05.commit -> the stage's mbarrier
-//   all threads   epilogue: tcgen05.ld the accumulator rows (warp w reads TMEM lanes 32*(w%4)...), cluster split-K
-//                 reduction through distributed shared memory (the CTAs of a cluster own consecutive slices of the
-//                 reduction axis; partial tiles are written into the leader's staging buffers), bias / padding mask,
-//                 16-byte stores.
+//   fp32 data, and the weight gradient (msda_proj_kernel):
+//     all threads global -> registers (16-byte loads, a ring of 2-4 reduction blocks in flight) -> [bf16 x 3 split] -> shared
+//                 memory in the 128-byte-swizzled UMMA layout (K-major or MN-major tiles, 64 reduction elements per block)
+//     thread 0    fence.proxy.async + tcgen05.mma for the staged block (four TMEM accumulators used round-robin),
+//                 tcgen05.commit -> the stage's mbarrier
+//   bf16 forward / data gradient (msda_proj_tma_kernel):
+//     warp 0 lane 0  producer: cp.async.bulk.tensor.2d boxes of the row-major matrices straight into the swizzled tiles (the
+//                 TMA swizzle IS the UMMA layout), full / empty mbarriers, four stages
+//     warp 1 lane 0  issues the MMAs and commits
+//   all threads   epilogue: tcgen05.ld the accumulator rows (warp w reads TMEM lanes 32*(w%4)...), sum of the four
+//                 accumulators, cluster split-K reduce-scatter through distributed shared memory (the CTAs of a cluster own
+//                 consecutive slices of the reduction axis and each reduces its share of the tile), bias / padding mask /
+//                 bias gradient, coalesced 16-byte stores.
 // The GEMMs here are small (100-375 rows, 256-512 columns, reduction 100-512): they are latency-bound, which is why
 // the reduction axis is split over a cluster -- more SMs stream the operands -- rather than tiles being made larger.
 #pragma once
