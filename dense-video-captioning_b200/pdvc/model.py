@@ -26,12 +26,13 @@ from torch import nn
 
 from ..ops.functions import CaptionAttendFunction, LSTMCellFunction, StepAttendRun, StepLinear, StepSampleRun, get_default_padding_mode
 from ..ops.modules import MSDeformAttnCap
-from .transformer import DeformableTransformer, inverse_sigmoid
+from .transformer import DeformableTransformer, _linear, inverse_sigmoid
 
 
 USE_FP32_SAMPLES = True    # bf16 autocast: caption-head samples (two projected-memory rows per sample) kept in fp32
 USE_FUSED_ATTEND = True    # one kernel each way for the soft attention over the samples (csrc/msda_capattend.cuh)
 USE_STEP_LSTM = True       # hoisted input projections + fused cell kernel instead of cuDNN's single-step LSTM
+USE_PROJ_MLP = True                  # hidden layers of the segment heads on the projection kernels (as the FFN layers)
 PARALLEL_HEADS = True                # class / count / segment heads of the decoder layers on one stream per layer
 PARALLEL_POSITION_EMBEDDING = True   # masks + position embeddings of the pyramid on a side stream beside the projections
 USE_STEP_SAMPLE_RUN = True # the word steps' sampler backward passes add into one grad_value / grad_reference buffer
@@ -187,7 +188,8 @@ class MLP(nn.Module):
 
     def forward(self, x):
         for i, layer in enumerate(self.layers):
-            x = layer(x)
+            # tcgen05 projection kernel where it applies (fp32 CUDA, widths multiples of 8), else nn.Linear
+            x = _linear(x, layer) if USE_PROJ_MLP else layer(x)
             if i < self.num_layers - 1:
                 x = F.relu(x)
         return x
