@@ -13,6 +13,7 @@
 Error behaviour follows the reference's host wrapper (ms_deform_attn_cuda.cu:28-38): non-contiguous
 or non-CUDA tensors raise RuntimeError; so do unsupported dtypes.
 """
+import contextlib
 import weakref
 
 import torch
@@ -468,6 +469,10 @@ class StepSampleRun:
         return True
 
 
+PROJ_WGRAD_SIDE_STREAM = True   # ProjLinearFunction.backward: weight gradient on a side stream beside the data gradient
+_SIDE_STREAMS = {}
+
+
 class ProjLinearFunction(Function):
     """The Linear projections of MSDeformAttn on the tcgen05 tensor cores (csrc/msda_proj.cuh).
 
@@ -533,18 +538,31 @@ class ProjLinearFunction(Function):
         code = _DTYPES[dt]
         dx = None
         with torch.cuda.device(dev):
+            dw0 = torch.empty((N0, K), dtype=torch.float32, device=dev)
+            db0 = torch.empty((N0,), dtype=torch.float32, device=dev) if has_b0 else None
+            dw1 = torch.empty((N1, K), dtype=torch.float32, device=dev) if N1 else None
+            db1 = torch.empty((N1,), dtype=torch.float32, device=dev) if (N1 and has_b1) else None
+            # the weight gradient needs dy and x, the data gradient dy and W: independent, both latency-bound on a fraction
+            # of the SMs -> the weight gradient runs on a side stream beside the data gradient (a parallel branch of a
+            # captured backward graph); joined before returning, so autograd sees every result on the caller's stream
+            side = main = None
+            if PROJ_WGRAD_SIDE_STREAM and ctx.needs_input_grad[0]:
+                main = torch.cuda.current_stream(dev)
+                side = _SIDE_STREAMS.get(dev)
+                if side is None:
+                    side = _SIDE_STREAMS[dev] = torch.cuda.Stream(dev)
+                side.wait_stream(main)
+            with (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):
+                rc = lib.msda_proj_wgrad(_ptr(dy0), _ptr(dy1), _ptr(x2), _ptr(mask), _ptr(dw0), _ptr(db0), _ptr(dw1), _ptr(db1),
+                                         rows, K, N0, N1, code, _stream(dev))
+            _lib.check(rc, "msda_proj_wgrad")
             if ctx.needs_input_grad[0]:
                 dx = torch.empty((rows, K), dtype=dt, device=dev)
                 rc = lib.msda_proj_dgrad(_ptr(dy0), _ptr(dy1), _ptr(w0), _ptr(w1), _ptr(mask), _ptr(dx), rows, K, N0, N1, code, _stream(dev))
                 _lib.check(rc, "msda_proj_dgrad")
                 dx = dx.view(xshape).to(xdtype)
-            dw0 = torch.empty((N0, K), dtype=torch.float32, device=dev)
-            db0 = torch.empty((N0,), dtype=torch.float32, device=dev) if has_b0 else None
-            dw1 = torch.empty((N1, K), dtype=torch.float32, device=dev) if N1 else None
-            db1 = torch.empty((N1,), dtype=torch.float32, device=dev) if (N1 and has_b1) else None
-            rc = lib.msda_proj_wgrad(_ptr(dy0), _ptr(dy1), _ptr(x2), _ptr(mask), _ptr(dw0), _ptr(db0), _ptr(dw1), _ptr(db1),
-                                     rows, K, N0, N1, code, _stream(dev))
-            _lib.check(rc, "msda_proj_wgrad")
+            if side is not None:
+                main.wait_stream(side)
         return (dx, dw0.to(w0dt), db0, dw1.to(w1dt) if dw1 is not None else None, db1, None)
 
 
