@@ -21,6 +21,10 @@ from ..functions.ms_deform_attn_func import MSDeformAttnFunction, MSDeformAttnFu
 USE_PROJ_GEMM = True
 
 
+PARALLEL_VALUE_PROJ = True    # value projection on a side stream beside the offsets / logits projection
+_VALUE_STREAMS = {}
+
+
 def _proj(x, lin0, lin1=None, row_mask=None):
     """lin0(x) [, lin1(x)] with the row mask applied to lin0's output; tcgen05 path when the shapes allow it."""
     w1 = lin1.weight if lin1 is not None else None
@@ -115,7 +119,22 @@ class _MSDeformFrontEnd(nn.Module):
         if reference_points.shape[-1] not in (1, 2):
             raise ValueError('Last dim of reference_points must be 1 or 2, but get {} instead.'.format(
                 reference_points.shape[-1]))
-        value = projected_value if projected_value is not None else self.project_value(input_flatten, input_padding_mask)
+        # value_proj(input) and the offsets / logits projection of the query are independent GEMMs, each latency-bound on a
+        # fraction of the SMs: the value projection runs on a side stream (a parallel branch of a captured graph, forward and
+        # -- autograd replays a node on the stream its forward ran on -- backward)
+        side = main = None
+        if projected_value is not None:
+            value = projected_value
+        elif PARALLEL_VALUE_PROJ and USE_PROJ_GEMM:
+            main = torch.cuda.current_stream(query.device)
+            side = _VALUE_STREAMS.get(query.device)
+            if side is None:
+                side = _VALUE_STREAMS[query.device] = torch.cuda.Stream(query.device)
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                value = self.project_value(input_flatten, input_padding_mask)
+        else:
+            value = self.project_value(input_flatten, input_padding_mask)
         logits = None
         if sampling_offsets is None and need_logits:
             sampling_offsets, logits = _proj(query, self.sampling_offsets, self.attention_weights)   # one GEMM
@@ -126,6 +145,10 @@ class _MSDeformFrontEnd(nn.Module):
         offsets = sampling_offsets.view(N, Len_q, self.n_heads, self.n_levels, self.n_points)
         if logits is not None:
             logits = logits.view(N, Len_q, self.n_heads, self.n_levels, self.n_points)
+        if side is not None:
+            main.wait_stream(side)
+            if not torch.cuda.is_current_stream_capturing():
+                value.record_stream(main)
         return value, offsets, logits
 
     def _locations_and_weights(self, reference_points, offsets, logits, input_spatial_shapes):
