@@ -33,6 +33,7 @@ USE_FP32_SAMPLES = True    # bf16 autocast: caption-head samples (two projected-
 USE_FUSED_ATTEND = True    # one kernel each way for the soft attention over the samples (csrc/msda_capattend.cuh)
 USE_STEP_LSTM = True       # hoisted input projections + fused cell kernel instead of cuDNN's single-step LSTM
 USE_PROJ_MLP = True                  # hidden layers of the segment heads on the projection kernels (as the FFN layers)
+PARALLEL_H2ATT = True                # word step: h2att(h) on a side stream beside the offsets -> sampler chain
 PARALLEL_HEADS = True                # class / count / segment heads of the decoder layers on one stream per layer
 PARALLEL_POSITION_EMBEDDING = True   # masks + position embeddings of the pyramid on a side stream beside the projections
 USE_STEP_SAMPLE_RUN = True # the word steps' sampler backward passes add into one grad_value / grad_reference buffer
@@ -224,6 +225,15 @@ class ShowAttendTellCore(nn.Module):
         # the top layer's hidden state, taken ONCE: every `state[0][-1]` is a select whose backward is a zero-fill + copy +
         # accumulation on the recurrence's critical path; StepLSTM hands the state over as 2-D tensors (no select at all)
         h_prev = state[0] if state[0].dim() == 2 else state[0][-1]
+        h2att = step_linears["h2att"] if step_linears is not None else self.h2att
+        # h2att(h) and the offsets -> sampler chain both hang on h only: h2att runs on a side stream beside the chain
+        hproj = side = main = None
+        if PARALLEL_H2ATT and step_linears is not None and h_prev.is_cuda and self.att_hid_size > 0:
+            main = torch.cuda.current_stream(h_prev.device)
+            side = self.__dict__.setdefault("_h2att_streams", {}).setdefault(str(h_prev.device), torch.cuda.Stream(h_prev.device))
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                hproj = h2att(h_prev)
         joint_query = torch.cat((h_prev.unsqueeze(0), query), 2)
         extra = {}
         if step_linears is not None:
@@ -240,13 +250,17 @@ class ShowAttendTellCore(nn.Module):
                                        padding_mask, projected_value=projected_value, **extra)   # (N*M, D', Lq, L, P)
             clip = clip.reshape(n, self.n_heads, -1, lq, k).permute(0, 3, 1, 4, 2)        # (N, Lq, M, L*P, D')
         clip = clip.reshape(n * lq, self.n_heads, k, -1)
-        h2att = step_linears["h2att"] if step_linears is not None else self.h2att
+        if side is not None:
+            main.wait_stream(side)
+            if not torch.cuda.is_current_stream_capturing():
+                hproj.record_stream(main)
         if clip.shape[-1] == self.att_feat_size + self.att_hid_size:
             # `projected_value` carried ctx2att(value) next to value (SentenceDecoder): interpolation weights sum to 1 in
             # border mode, so sampling the projected rows IS ctx2att of the sampled rows (LSTM_DSA.py:247) without the
             # per-word GEMM, its two backward GEMMs and the per-word weight-gradient accumulation
             if USE_FUSED_ATTEND and CaptionAttendFunction.supported(clip, k, self.att_feat_size):
-                attended = CaptionAttendFunction.apply(clip.reshape(n * lq * self.n_heads, k, -1), h2att(h_prev),
+                attended = CaptionAttendFunction.apply(clip.reshape(n * lq * self.n_heads, k, -1),
+                                                       hproj if hproj is not None else h2att(h_prev),
                                                        self.alpha_net.weight, self.alpha_net.bias, self.att_feat_size,
                                                        step_linears.get("attend_run") if step_linears else None)
                 clip = None
@@ -255,7 +269,7 @@ class ShowAttendTellCore(nn.Module):
         else:
             ctx = self.ctx2att(clip)
         if clip is not None:
-            scores = ctx + h2att(h_prev)[:, None, None, :]
+            scores = ctx + (hproj if hproj is not None else h2att(h_prev))[:, None, None, :]
             scores = self.alpha_net(torch.tanh(scores)).view(-1, k)
             weight = F.softmax(scores, dim=1)
             attended = torch.bmm(weight.unsqueeze(1), clip.reshape(-1, k, self.att_feat_size)).squeeze(1)
