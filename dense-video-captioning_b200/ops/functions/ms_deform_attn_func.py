@@ -21,6 +21,7 @@ from torch.autograd import Function
 from torch.autograd.function import once_differentiable
 
 from ... import _lib
+from ..._streams import branch_stream
 
 _DTYPES = {torch.float32: _lib.F32, torch.bfloat16: _lib.BF16, torch.float64: _lib.F64}
 _PAD = {"border": _lib.PAD_BORDER, "zeros": _lib.PAD_ZEROS}
@@ -470,7 +471,6 @@ class StepSampleRun:
 
 
 PROJ_WGRAD_SIDE_STREAM = True   # ProjLinearFunction.backward: weight gradient on a side stream beside the data gradient
-_SIDE_STREAMS = {}
 
 
 class ProjLinearFunction(Function):
@@ -548,9 +548,7 @@ class ProjLinearFunction(Function):
             side = main = None
             if PROJ_WGRAD_SIDE_STREAM and ctx.needs_input_grad[0]:
                 main = torch.cuda.current_stream(dev)
-                side = _SIDE_STREAMS.get(dev)
-                if side is None:
-                    side = _SIDE_STREAMS[dev] = torch.cuda.Stream(dev)
+                side = branch_stream(dev, "proj_wgrad")
                 side.wait_stream(main)
             with (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):
                 rc = lib.msda_proj_wgrad(_ptr(dy0), _ptr(dy1), _ptr(x2), _ptr(mask), _ptr(dw0), _ptr(db0), _ptr(dw1), _ptr(db1),

@@ -14,6 +14,7 @@ from torch import nn
 from torch.nn.init import constant_, xavier_uniform_
 
 from ... import _lib
+from ..._streams import branch_stream
 from ..functions.ms_deform_attn_func import MSDeformAttnFunction, MSDeformAttnFusedFunction, ProjLinearFunction
 
 # The module's Linear projections on the hand-written tcgen05 GEMMs (csrc/msda_proj.cuh; value_proj with its padding
@@ -22,7 +23,6 @@ USE_PROJ_GEMM = True
 
 
 PARALLEL_VALUE_PROJ = True    # value projection on a side stream beside the offsets / logits projection
-_VALUE_STREAMS = {}
 
 
 def _proj(x, lin0, lin1=None, row_mask=None):
@@ -127,9 +127,7 @@ class _MSDeformFrontEnd(nn.Module):
             value = projected_value
         elif PARALLEL_VALUE_PROJ and USE_PROJ_GEMM:
             main = torch.cuda.current_stream(query.device)
-            side = _VALUE_STREAMS.get(query.device)
-            if side is None:
-                side = _VALUE_STREAMS[query.device] = torch.cuda.Stream(query.device)
+            side = branch_stream(query.device, "value_proj")
             side.wait_stream(main)
             with torch.cuda.stream(side):
                 value = self.project_value(input_flatten, input_padding_mask)

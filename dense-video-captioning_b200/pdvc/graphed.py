@@ -30,6 +30,7 @@ import torch
 from scipy.optimize import linear_sum_assignment
 from torch import nn
 
+from .._streams import branch_stream
 from ..ops.functions.matching import linear_sum_assignment_cuda, pdvc_match_cuda
 from .model import caption_steps
 
@@ -202,12 +203,9 @@ class LossStage(nn.Module):
         self.level_lengths = list(level_lengths)
         self.parallel_layers = True
         self.batch_layers = True
-        self.__dict__["_streams"] = []
 
     def _side_streams(self, n, device):
-        while len(self._streams) < n:
-            self._streams.append(torch.cuda.Stream(device))
-        return self._streams[:n]
+        return [branch_stream(device, "caption_loop", i) for i in range(n)]
 
     def _caption_losses_per_layer(self, hs, init_reference, inter_references, others, cap_tensor, cap_mask, q_idx, t_idx):
         """Caption heads that differ per layer (share_caption_head=0) or layers with different word-step counts."""

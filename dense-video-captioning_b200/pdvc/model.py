@@ -25,6 +25,7 @@ import torch.nn.functional as F
 from torch import nn
 
 from ..ops.functions import CaptionAttendFunction, LSTMCellFunction, StepAttendRun, StepLinear, StepSampleRun, get_default_padding_mode
+from .._streams import branch_stream
 from ..ops.modules import MSDeformAttnCap
 from .transformer import DeformableTransformer, _linear, inverse_sigmoid
 
@@ -161,7 +162,7 @@ class BaseEncoder(nn.Module):
         side = main = None
         if x.is_cuda and PARALLEL_POSITION_EMBEDDING:
             main = torch.cuda.current_stream(x.device)
-            side = self.__dict__.setdefault("_side_stream", {}).setdefault(str(x.device), torch.cuda.Stream(x.device))
+            side = branch_stream(x.device, "position_embedding")
             side.wait_stream(main)
         with (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):
             dur = self.pos_embed.duration_embedding(duration, mask.device)
@@ -230,7 +231,7 @@ class ShowAttendTellCore(nn.Module):
         hproj = side = main = None
         if PARALLEL_H2ATT and step_linears is not None and h_prev.is_cuda and self.att_hid_size > 0:
             main = torch.cuda.current_stream(h_prev.device)
-            side = self.__dict__.setdefault("_h2att_streams", {}).setdefault(str(h_prev.device), torch.cuda.Stream(h_prev.device))
+            side = branch_stream(h_prev.device, "h2att")
             side.wait_stream(main)
             with torch.cuda.stream(side):
                 hproj = h2att(h_prev)
@@ -492,10 +493,7 @@ class PDVC(nn.Module):
         side, main = [], None
         if hs.is_cuda and PARALLEL_HEADS and n_layers > 1:
             main = torch.cuda.current_stream(hs.device)
-            pool = self.__dict__.setdefault("_head_streams", {}).setdefault(str(hs.device), [])
-            while len(pool) < n_layers - 1:
-                pool.append(torch.cuda.Stream(hs.device))
-            side = pool[:n_layers - 1]
+            side = [branch_stream(hs.device, "heads", i) for i in range(n_layers - 1)]
             for s_ in side:
                 s_.wait_stream(main)
         for lid in range(n_layers):

@@ -23,6 +23,8 @@ from dataclasses import replace
 import numpy as np
 import torch
 
+from .._streams import branch_stream
+
 from .model import PDVCConfig, build
 
 CONFIGS = {
@@ -219,7 +221,7 @@ class Trainer:
                 for p, v in zip(group, views):
                     p.grad = v
             if self.world_size > 1:
-                self._comm_stream = torch.cuda.Stream(self.device)
+                self._comm_stream = branch_stream(self.device, "gradient_allreduce")
                 self.net.after_backward[2] = lambda: self._issue_bucket(0, side=True)
                 self.net.after_backward[1] = lambda: self._issue_bucket(1, side=False)
 
