@@ -58,24 +58,50 @@ __device__ __forceinline__ float block_sum(float v, float *scratch)
     return t;   // valid in thread 0
 }
 
-// partials[blockIdx.x] = sum of g^2 over this block's grid-stride share of all segments
+// partials[blockIdx.x] = sum of g^2 over this block's grid-stride share of all segments (16-byte loads where the segment
+// is aligned, four in flight per thread: the pass is a pure HBM read)
 __global__ void __launch_bounds__(kThreads) msda_sumsq_kernel(const Segment *segs, int n_segs, float *partials)
 {
     __shared__ float scratch[kThreads / 32];
     float acc = 0.f;
+    const long long stride = (long long)gridDim.x * kThreads;
+    const long long first = (long long)blockIdx.x * kThreads + threadIdx.x;
     for (int s = 0; s < n_segs; ++s) {
         const float *g = segs[s].g;
         const long long n = segs[s].n;
-        const long long stride = (long long)gridDim.x * kThreads;
-        long long i = (long long)blockIdx.x * kThreads + threadIdx.x;
-        for (; i + 3 * stride < n; i += 4 * stride) {           // four independent loads in flight
-            const float a = g[i], b = g[i + stride], c = g[i + 2 * stride], d = g[i + 3 * stride];
-            acc = fmaf(a, a, acc); acc = fmaf(b, b, acc); acc = fmaf(c, c, acc); acc = fmaf(d, d, acc);
+        long long done = 0;
+        if ((reinterpret_cast<uintptr_t>(g) & 15u) == 0) {
+            const float4 *g4 = reinterpret_cast<const float4 *>(g);
+            const long long n4 = n >> 2;
+            long long i = first;
+            for (; i + 3 * stride < n4; i += 4 * stride) {
+                const float4 a = g4[i], b = g4[i + stride], c = g4[i + 2 * stride], d = g4[i + 3 * stride];
+                acc = fmaf(a.x, a.x, fmaf(a.y, a.y, fmaf(a.z, a.z, fmaf(a.w, a.w, acc))));
+                acc = fmaf(b.x, b.x, fmaf(b.y, b.y, fmaf(b.z, b.z, fmaf(b.w, b.w, acc))));
+                acc = fmaf(c.x, c.x, fmaf(c.y, c.y, fmaf(c.z, c.z, fmaf(c.w, c.w, acc))));
+                acc = fmaf(d.x, d.x, fmaf(d.y, d.y, fmaf(d.z, d.z, fmaf(d.w, d.w, acc))));
+            }
+            for (; i < n4; i += stride) {
+                const float4 a = g4[i];
+                acc = fmaf(a.x, a.x, fmaf(a.y, a.y, fmaf(a.z, a.z, fmaf(a.w, a.w, acc))));
+            }
+            done = n4 << 2;
         }
-        for (; i < n; i += stride) { const float a = g[i]; acc = fmaf(a, a, acc); }
+        for (long long i = done + first; i < n; i += stride) { const float a = g[i]; acc = fmaf(a, a, acc); }
     }
     const float t = block_sum(acc, scratch);
     if (threadIdx.x == 0) partials[blockIdx.x] = t;
+}
+
+// torch's fused-Adam rule for one element (fused_adam_utils.cuh, ADAM_MODE::ORIGINAL, no amsgrad)
+__device__ __forceinline__ void adam_update(float &p, float &m, float &v, float grad, float coef, const Hyper &h)
+{
+    float g = grad * coef;
+    if (h.weight_decay != 0.f) g = fmaf(h.weight_decay, p, g);        // Adam's L2 form: grad += wd * param
+    m = fmaf(h.one_minus_beta1, g - m, m);                             // lerp(m, g, 1 - beta1)
+    v = fmaf(h.beta2, v, h.one_minus_beta2 * g * g);
+    const float denom = sqrtf(v) / h.bias_correction2_sqrt + h.eps;
+    p -= h.step_size * m / denom;
 }
 
 __global__ void __launch_bounds__(kThreads) msda_adam_kernel(const Chunk *chunks, int n_chunks, const float *partials,
@@ -96,23 +122,32 @@ __global__ void __launch_bounds__(kThreads) msda_adam_kernel(const Chunk *chunks
         __syncthreads();
         coef = coef_s;
     }
-    const float step_size = h.step_size;
-    const float one_minus_b1 = h.one_minus_beta1, one_minus_b2 = h.one_minus_beta2;
     for (int c = blockIdx.x; c < n_chunks; c += gridDim.x) {
         const Chunk ck = chunks[c];
-#pragma unroll 4
-        for (int i = threadIdx.x; i < ck.n; i += kThreads) {
-            float p = ck.param[i];
-            float g = ck.grad[i] * coef;
-            if (h.weight_decay != 0.f) g = fmaf(h.weight_decay, p, g);        // Adam's L2 form: grad += wd * param
-            float m = ck.exp_avg[i], v = ck.exp_avg_sq[i];
-            m = fmaf(one_minus_b1, g - m, m);                                   // lerp(m, g, 1 - beta1)
-            v = fmaf(h.beta2, v, one_minus_b2 * g * g);
-            const float denom = sqrtf(v) / h.bias_correction2_sqrt + h.eps;
-            p -= step_size * m / denom;
-            ck.param[i] = p;
-            ck.exp_avg[i] = m;
-            ck.exp_avg_sq[i] = v;
+        int done = 0;
+        if (((reinterpret_cast<uintptr_t>(ck.param) | reinterpret_cast<uintptr_t>(ck.grad) | reinterpret_cast<uintptr_t>(ck.exp_avg) |
+              reinterpret_cast<uintptr_t>(ck.exp_avg_sq)) & 15u) == 0) {
+            // 16-byte path: the update moves 28 bytes per parameter and nothing else -- keep the loads wide and many in flight
+            float4 *p4 = reinterpret_cast<float4 *>(ck.param), *m4 = reinterpret_cast<float4 *>(ck.exp_avg),
+                   *v4 = reinterpret_cast<float4 *>(ck.exp_avg_sq);
+            const float4 *g4 = reinterpret_cast<const float4 *>(ck.grad);
+            const int n4 = ck.n >> 2;
+#pragma unroll 2
+            for (int i = threadIdx.x; i < n4; i += kThreads) {
+                float4 p = p4[i], m = m4[i], v = v4[i];
+                const float4 g = g4[i];
+                adam_update(p.x, m.x, v.x, g.x, coef, h);
+                adam_update(p.y, m.y, v.y, g.y, coef, h);
+                adam_update(p.z, m.z, v.z, g.z, coef, h);
+                adam_update(p.w, m.w, v.w, g.w, coef, h);
+                p4[i] = p; m4[i] = m; v4[i] = v;
+            }
+            done = n4 << 2;
+        }
+        for (int i = done + threadIdx.x; i < ck.n; i += kThreads) {
+            float p = ck.param[i], m = ck.exp_avg[i], v = ck.exp_avg_sq[i];
+            adam_update(p, m, v, ck.grad[i], coef, h);
+            ck.param[i] = p; ck.exp_avg[i] = m; ck.exp_avg_sq[i] = v;
         }
     }
 }

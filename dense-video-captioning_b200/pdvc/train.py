@@ -208,11 +208,13 @@ class Trainer:
         groups = [[p for p in self.params if id(p) in first], [p for p in self.params if id(p) not in first]]
         self._buckets = []
         for group in groups:
-            flat = torch.zeros(sum(p.numel() for p in group), dtype=self.params[0].dtype, device=self.device)
-            views, offset = [], 0
+            # every parameter's slot starts on a 16-byte boundary (the fused optimizer's vector path, pdvc/optim.py)
+            starts, offset = [], 0
             for p in group:
-                views.append(flat[offset:offset + p.numel()].view_as(p))
-                offset += p.numel()
+                starts.append(offset)
+                offset += (p.numel() + 3) // 4 * 4
+            flat = torch.zeros(offset, dtype=self.params[0].dtype, device=self.device)
+            views = [flat[o:o + p.numel()].view_as(p) for o, p in zip(starts, group)]
             self._buckets.append((flat, group, views))
         self._sinks_live = self.mode == "graphs"
         if self._sinks_live:
@@ -255,7 +257,7 @@ class Trainer:
         after backward -- the exchange pattern without the overlap."""
         for flat, group, views in self._buckets:
             grads = [p.grad if p.grad is not None else torch.zeros_like(p) for p in group]
-            torch.cat([g.reshape(-1) for g in grads], out=flat)
+            torch._foreach_copy_(views, grads)       # slots are 16-byte aligned: not a plain concatenation
             self._reduce_mean(flat)
             for p, view in zip(group, views):
                 p.grad = view
