@@ -130,12 +130,26 @@ __global__ void __launch_bounds__(32) msda_lsap_kernel(const Args a, const Sourc
 
     // ---- stage + validate ----
     int invalid = 0;
-    for (int k = lane; k < a.R * a.C; k += 32) {
-        const int r = k / a.C, q = k - r * a.C;
-        const float c = source(cost, b, k, r, q);
-        if (Source::kWrites) cost[k] = c;
-        invalid |= (c != c) || (c == -CUDART_INF_F);
-        if (a.staged) cs[transposed ? q * nc + r : k] = c;
+    // four entries per lane and pass: all their (dependent: label -> logit) global loads are in flight together -- the
+    // matrices are small and this loop is a chain of memory round trips
+    for (int k0 = lane; k0 < a.R * a.C; k0 += 32 * kScanBatch) {
+        float c[kScanBatch];
+#pragma unroll
+        for (int t = 0; t < kScanBatch; ++t) {
+            const int k = k0 + 32 * t;
+            const int kk = k < a.R * a.C ? k : k0;
+            const int r = kk / a.C, q = kk - r * a.C;
+            c[t] = source(cost, b, kk, r, q);
+        }
+#pragma unroll
+        for (int t = 0; t < kScanBatch; ++t) {
+            const int k = k0 + 32 * t;
+            if (k >= a.R * a.C) continue;
+            const int r = k / a.C, q = k - r * a.C;
+            if (Source::kWrites) cost[k] = c[t];
+            invalid |= (c[t] != c[t]) || (c[t] == -CUDART_INF_F);
+            if (a.staged) cs[transposed ? q * nc + r : k] = c[t];
+        }
     }
     invalid = __any_sync(kFullMask, invalid);
     if (Source::kWrites) __threadfence_block();       // an unstaged search reads the matrix back from global memory
