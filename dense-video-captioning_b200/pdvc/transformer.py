@@ -23,7 +23,7 @@ from ..ops.modules.ms_deform_attn import _proj
 # (yc2 shape: 5.87 -> 5.83 ms/step); under bf16 autocast cuBLAS' tensor-core GEMMs are faster for these plain layers
 # (7.76 vs 7.82 ms/step, tools/pdvc_ab.py).  False: torch's library GEMMs always.
 USE_PROJ_FFN = True
-FUSED_SELF_ATTENTION = True     # decoder self-attention without materialised attention weights (CUDA)
+FUSED_SELF_ATTENTION = False    # decoder self-attention without materialised attention weights (CUDA)
 
 
 def _linear(x, lin):
