@@ -23,7 +23,6 @@ from ..ops.modules.ms_deform_attn import _proj
 # (yc2 shape: 5.87 -> 5.83 ms/step); under bf16 autocast cuBLAS' tensor-core GEMMs are faster for these plain layers
 # (7.76 vs 7.82 ms/step, tools/pdvc_ab.py).  False: torch's library GEMMs always.
 USE_PROJ_FFN = True
-FUSED_SELF_ATTENTION = False    # decoder self-attention without materialised attention weights (CUDA)
 
 
 def _linear(x, lin):
@@ -109,10 +108,9 @@ class DeformableTransformerDecoderLayer(nn.Module):
                 src_padding_mask=None, query_mask=None):
         qk = (tgt if query_pos is None else tgt + query_pos).transpose(0, 1)
         key_padding = None if query_mask is None else ~query_mask
-        # the attention weights are discarded (deformable_transformer.py:257 takes [0]): on CUDA they are not materialised
-        # (need_weights=False -> fused scaled-dot-product attention instead of bmm / softmax / dropout / bmm / head average)
-        attended = self.self_attn(qk, qk, tgt.transpose(0, 1), key_padding_mask=key_padding,
-                                  need_weights=not (FUSED_SELF_ATTENTION and qk.is_cuda))[0].transpose(0, 1)
+        # (need_weights=False -- torch's fused scaled-dot-product attention instead of bmm / softmax / dropout / bmm -- was
+        # measured: 4.16 -> 4.20 ms/step at 100 queries, not faster; profiles/r2_notes.md)
+        attended = self.self_attn(qk, qk, tgt.transpose(0, 1), key_padding_mask=key_padding)[0].transpose(0, 1)
         tgt = self.norm2(tgt + self.dropout2(attended))
         query = tgt if query_pos is None else tgt + query_pos
         sampled = self.cross_attn(query, reference_points, src, src_temporal_shapes, level_start_index, src_padding_mask)
