@@ -30,15 +30,16 @@ from ..ops.modules import MSDeformAttnCap
 from .transformer import DeformableTransformer, _linear, inverse_sigmoid
 
 
-USE_FP32_SAMPLES = True    # bf16 autocast: caption-head samples (two projected-memory rows per sample) kept in fp32
-USE_FUSED_ATTEND = True    # one kernel each way for the soft attention over the samples (csrc/msda_capattend.cuh)
-USE_STEP_LSTM = True       # hoisted input projections + fused cell kernel instead of cuDNN's single-step LSTM
+# Module-level switches (each an exact regrouping of the reference's expressions; tools/pdvc_ab.py A/Bs one at a time)
+USE_FP32_SAMPLES = True              # bf16 autocast: caption-head samples (two projected-memory rows per sample) kept in fp32
+USE_FUSED_ATTEND = True              # one kernel each way for the soft attention over the samples (csrc/msda_capattend.cuh)
+USE_STEP_LSTM = True                 # hoisted input projections + fused cell kernel instead of cuDNN's single-step LSTM
+USE_STEP_LINEAR = True               # few-row kernels + deferred weight gradients for the Linear layers on the caption recurrence
+USE_STEP_SAMPLE_RUN = True           # word steps: sampler / alpha_net gradient sums formed once per decoding run
 USE_PROJ_MLP = True                  # hidden layers of the segment heads on the projection kernels (as the FFN layers)
 PARALLEL_H2ATT = True                # word step: h2att(h) on a side stream beside the offsets -> sampler chain
 PARALLEL_HEADS = True                # class / count / segment heads of the decoder layers on one stream per layer
 PARALLEL_POSITION_EMBEDDING = True   # masks + position embeddings of the pyramid on a side stream beside the projections
-USE_STEP_SAMPLE_RUN = True # the word steps' sampler backward passes add into one grad_value / grad_reference buffer
-USE_STEP_LINEAR = True     # few-row kernels + deferred weight gradients for the Linear layers on the caption recurrence
 
 
 @dataclass

@@ -2,8 +2,8 @@
 
 What the reference does per iteration (train.py:163-194): move the batch to the device, forward with the criterion,
 weighted loss sum, backward, clip_grad_norm_(100), Adam step -- batch size 1 video, with a `cuda.synchronize()` before
-and after every iteration.  Same step here, minus the two forced synchronisations, with the inputs copied from pinned
-host memory each step, and -- new, the reference never wraps PDVC in DDP (SURVEY finding 0.8) -- one process per GPU
+and after every iteration.  Same step here, minus the two forced synchronisations (and, in 'graphs' mode, minus the
+host round trip of the Hungarian matching: pdvc/graphed.py), with the inputs copied from pinned host memory each step, and -- new, the reference never wraps PDVC in DDP (SURVEY finding 0.8) -- one process per GPU
 with an NCCL all-reduce (mean) of the gradients.  Three exchange modes (`Trainer(sync=...)`):
   'overlap' (default)  two flat buckets; the caption-head bucket is reduced on a side stream WHILE the stage-1 backward
                        graph replays, the rest right after it; gradients reach the buckets through copies captured in
@@ -24,7 +24,6 @@ import numpy as np
 import torch
 
 from .._streams import branch_stream
-
 from .model import PDVCConfig, build
 
 CONFIGS = {
