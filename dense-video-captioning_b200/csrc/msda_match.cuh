@@ -11,7 +11,7 @@
 // columns is conflict-free) when it fits.  The scan over the remaining columns is split over the lanes (lane k takes the
 // k-th, k+32-th, ... remaining column, four at a time) and merged with a comparator that reproduces the sequential scan.
 // A search step is a chain of shared-memory round trips, float64 adds and a 5-round warp reduction, ~0.5 us: the matrices of
-// a PDVC step (100 queries x 6 events per decoder layer) take < 10 us inside stage 1's graph, 4 x (100 x 30) 78 us,
+// a PDVC step (2 x 100 queries x 6 events, costs formed in the kernel) take ~30 us inside stage 1's graph, 4 x (100 x 30) 78 us,
 // 1024 x 64 0.64 ms (tools/match_gap_probe.py) -- latency-bound scalar work; the point is that the host no longer waits.
 #pragma once
 #include <cuda_runtime.h>
