@@ -7,7 +7,7 @@
 // in float64 like scipy, with scipy's scan order and tie rule, so that the assignment is the one scipy returns also when
 // costs tie (oracle/lsap_port.py is the line-by-line CPU restatement; tests/test_match.py pins both against scipy).
 //
-// One CTA of 32 threads per matrix; all state in shared memory; the cost matrix is staged (transposed so that the scan over
+// One CTA per matrix: four warps form / stage the matrix, then one warp runs the search; all state in shared memory; the cost matrix is staged (transposed so that the scan over
 // columns is conflict-free) when it fits.  The scan over the remaining columns is split over the lanes (lane k takes the
 // k-th, k+32-th, ... remaining column, four at a time) and merged with a comparator that reproduces the sequential scan.
 // A search step is a chain of shared-memory round trips, float64 adds and a 5-round warp reduction, ~0.5 us: the matrices of
@@ -104,10 +104,11 @@ struct PdvcCost {
     }
 };
 
+constexpr int kStageThreads = 128;   // the block: all four warps form / stage the cost matrix, warp 0 alone runs the search
 constexpr int kScanBatch = 4;   // columns per lane whose loads are issued together (the scan is a chain of shared-memory round trips)
 
 template <class Source>
-__global__ void __launch_bounds__(32) msda_lsap_kernel(const Args a, const Source source)
+__global__ void __launch_bounds__(kStageThreads) msda_lsap_kernel(const Args a, const Source source)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x;
@@ -132,18 +133,18 @@ __global__ void __launch_bounds__(32) msda_lsap_kernel(const Args a, const Sourc
     int invalid = 0;
     // four entries per lane and pass: all their (dependent: label -> logit) global loads are in flight together -- the
     // matrices are small and this loop is a chain of memory round trips
-    for (int k0 = lane; k0 < a.R * a.C; k0 += 32 * kScanBatch) {
+    for (int k0 = threadIdx.x; k0 < a.R * a.C; k0 += kStageThreads * kScanBatch) {
         float c[kScanBatch];
 #pragma unroll
         for (int t = 0; t < kScanBatch; ++t) {
-            const int k = k0 + 32 * t;
+            const int k = k0 + kStageThreads * t;
             const int kk = k < a.R * a.C ? k : k0;
             const int r = kk / a.C, q = kk - r * a.C;
             c[t] = source(cost, b, kk, r, q);
         }
 #pragma unroll
         for (int t = 0; t < kScanBatch; ++t) {
-            const int k = k0 + 32 * t;
+            const int k = k0 + kStageThreads * t;
             if (k >= a.R * a.C) continue;
             const int r = k / a.C, q = k - r * a.C;
             if (Source::kWrites) cost[k] = c[t];
@@ -151,8 +152,9 @@ __global__ void __launch_bounds__(32) msda_lsap_kernel(const Args a, const Sourc
             if (a.staged) cs[transposed ? q * nc + r : k] = c[t];
         }
     }
-    invalid = __any_sync(kFullMask, invalid);
     if (Source::kWrites) __threadfence_block();       // an unstaged search reads the matrix back from global memory
+    invalid = __syncthreads_or(invalid);              // the matrix is complete; the search below is one warp's work
+    if (threadIdx.x >= 32) return;
     for (int j = lane; j < nc; j += 32) { v[j] = 0.0; row4col[j] = -1; }
     for (int i = lane; i < nr; i += 32) { u[i] = 0.0; col4row[i] = -1; }
     __syncwarp();

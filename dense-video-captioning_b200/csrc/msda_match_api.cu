@@ -17,7 +17,7 @@ template <class Source> int launch_lsap(Args a, const Source &src, int B, int nr
     if (smem > 48 * 1024)
         if (cudaError_t e = cudaFuncSetAttribute(msda_lsap_kernel<Source>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))
             return (int)e;
-    msda_lsap_kernel<Source><<<B, 32, smem, static_cast<cudaStream_t>(stream)>>>(a, src);
+    msda_lsap_kernel<Source><<<B, kStageThreads, smem, static_cast<cudaStream_t>(stream)>>>(a, src);
     ++g_launches;
     g_path = MSDA_PATH_MATCH;
     return (int)cudaGetLastError();
