@@ -157,3 +157,22 @@ def test_bench_helpers():
         assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
     b = bench.offset_bias(8, 4, 4)
     assert torch.equal(b.reshape(-1), dvc.MSDeformAttn(512, 4, 8, 4).sampling_offsets.bias.detach())
+
+
+def test_training_harness_kernels_have_no_cpu_path():
+    """The device-side matcher and the fused optimizer refuse CPU tensors instead of falling back (scipy / torch.optim.Adam
+    are the host-side tools; the trainer picks them itself when it runs on the CPU)."""
+    import pytest
+    import torch
+    from dense_video_captioning_b200.ops.functions import linear_sum_assignment_cuda, lsap_supported, pdvc_match_cuda
+    from dense_video_captioning_b200.pdvc.optim import FlatClipAdam
+    costs = torch.zeros(2, 5, 3)
+    assert not lsap_supported(costs)
+    with pytest.raises(RuntimeError):
+        linear_sum_assignment_cuda(costs)
+    with pytest.raises(RuntimeError):
+        pdvc_match_cuda(torch.zeros(2, 5, 1), torch.zeros(2, 5, 2), torch.zeros(3, dtype=torch.long), torch.zeros(3, 2), 1, 1, 1, 0.25, 2.0)
+    p = torch.zeros(4, requires_grad=True)
+    flat = torch.zeros(4)
+    with pytest.raises(RuntimeError):
+        FlatClipAdam([(flat, [p], [flat.view_as(p)])])
